@@ -1,0 +1,263 @@
+// Native data-parallel MLP trainer: the B200 form of the reference's training application
+// sw/mlp_mpi_example_f32.cpp:191-881 (main).  One process per GPU; per iteration (the hot loop at
+// :701-788):
+//   forward  L tcgen05 GEMMs (+bias/ReLU/mask epilogue)              :707-710
+//   loss     fused softmax + cross-entropy fwd/bwd                   :718-728
+//   backward for l = L-1 .. 0:  dW_l (fp32, straight into the flat gradient bucket) on the wgrad
+//            stream, dX_l on the main stream, then the fused all-reduce + SGD of bucket l on the
+//            comm stream - layer l's reduction overlaps layer l-1's GEMMs like request[i%2] does in
+//            the reference (:735-788), but with up to L requests in flight instead of 2.
+// The next iteration's forward of layer l waits only on layer l's update event.
+// Weights are flat fp32 [C[l+1]][C[l]] buffers in the symmetric heap (the reference's
+// fpga.allocBuffer'd fil_libxsmm, :396-401) with a bf16 shadow for the tensor cores.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/ainic.h"
+
+namespace {
+
+struct Layer {
+  int in = 0, out = 0;
+  float* w = nullptr;            // fp32 master, symmetric heap
+  float* g = nullptr;            // fp32 gradient bucket, symmetric heap
+  __nv_bfloat16* wb = nullptr;   // bf16 shadow
+  float* bias = nullptr;         // fp32 [out]
+  float* dbias = nullptr;
+  uint8_t* mask = nullptr;       // [mb][out] ReLU mask
+  cudaEvent_t dy_ready = nullptr;   // dact[l+1] complete (main stream)
+  cudaEvent_t dw_ready = nullptr;   // gradient bucket complete (wgrad stream)
+  cudaEvent_t updated = nullptr;    // weights + shadow updated (comm stream)
+  cudaEvent_t dx_done = nullptr;    // backward-data GEMM finished reading the shadow (main stream)
+};
+
+}  // namespace
+
+struct ainic_mlp {
+  ainic_comm_t* comm = nullptr;
+  int nlayers = 0, mb = 0, fuse = 0;
+  float lr = 0.1f, loss_weight = 0.1f;
+  int codec = AINIC_CODEC_F32, bfp_mode = AINIC_BFP_CLEAN, algo = AINIC_ALGO_AUTO;
+  int comm_ctas = 0, gemm_ctas = 0, wgrad_ctas = 0;
+  std::vector<Layer> layers;
+  std::vector<__nv_bfloat16*> act;   // act[0..L]   [mb][C[l]]
+  std::vector<__nv_bfloat16*> dact;  // dact[1..L]  [mb][C[l]]
+  float* loss_sum = nullptr;         // device scalar
+  cudaStream_t wgrad_stream = nullptr, comm_stream = nullptr;
+  cudaEvent_t fwd_done = nullptr;
+  bool first_step = true;
+  unsigned long long launches = 0;
+};
+
+static int fail(const char* what) {
+  fprintf(stderr, "ainic_mlp: %s failed: %s\n", what, cudaGetErrorString(cudaGetLastError()));
+  return AINIC_ERR_CUDA;
+}
+#define TRY_CUDA(x) do { if ((x) != cudaSuccess) return fail(#x); } while (0)
+#define TRY(x) do { int _rc = (x); if (_rc) return _rc; } while (0)
+
+extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlayers, const int* sizes, int mb, int fuse,
+                                float lr, float loss_weight, int codec, int bfp_mode, int algo) {
+  if (!out || !comm || nlayers < 1 || !sizes || mb < 1) return AINIC_ERR_ARG;
+  for (int i = 0; i <= nlayers; ++i)
+    if (sizes[i] < 8 || sizes[i] % 8) return AINIC_ERR_ARG;
+  ainic_mlp* m = new ainic_mlp();
+  m->comm = comm;
+  m->nlayers = nlayers;
+  m->mb = mb;
+  m->fuse = fuse;
+  m->lr = lr;
+  m->loss_weight = loss_weight;
+  m->codec = codec;
+  m->bfp_mode = bfp_mode;
+  m->algo = algo;
+  if (const char* e = getenv("AINIC_COMM_CTAS")) m->comm_ctas = atoi(e);
+  if (const char* e = getenv("AINIC_GEMM_CTAS")) m->gemm_ctas = atoi(e);
+  if (const char* e = getenv("AINIC_WGRAD_CTAS")) m->wgrad_ctas = atoi(e);
+  m->layers.resize(nlayers);
+  m->act.resize(nlayers + 1);
+  m->dact.resize(nlayers + 1);
+  int prio_lo = 0, prio_hi = 0;
+  cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+  TRY_CUDA(cudaStreamCreateWithPriority(&m->wgrad_stream, cudaStreamNonBlocking, prio_lo));
+  TRY_CUDA(cudaStreamCreateWithPriority(&m->comm_stream, cudaStreamNonBlocking, prio_hi));
+  TRY_CUDA(cudaEventCreateWithFlags(&m->fwd_done, cudaEventDisableTiming));
+  TRY_CUDA(cudaMalloc(&m->loss_sum, 256));
+  for (int l = 0; l <= nlayers; ++l) {
+    TRY_CUDA(cudaMalloc(&m->act[l], (size_t)mb * sizes[l] * 2));
+    if (l > 0) TRY_CUDA(cudaMalloc(&m->dact[l], (size_t)mb * sizes[l] * 2));
+  }
+  // Symmetric allocations, identical order on every rank.
+  for (int l = 0; l < nlayers; ++l) {
+    Layer& L = m->layers[l];
+    L.in = sizes[l];
+    L.out = sizes[l + 1];
+    const size_t n = (size_t)L.in * L.out;
+    L.w = static_cast<float*>(ainic_comm_alloc(comm, n * 4, 4096));
+    L.g = static_cast<float*>(ainic_comm_alloc(comm, n * 4, 4096));
+    if (!L.w || !L.g) return AINIC_ERR_ARG;
+    TRY_CUDA(cudaMalloc(&L.wb, n * 2));
+    TRY_CUDA(cudaMalloc(&L.bias, (size_t)L.out * 4));
+    TRY_CUDA(cudaMalloc(&L.dbias, (size_t)L.out * 4));
+    TRY_CUDA(cudaMemset(L.bias, 0, (size_t)L.out * 4));
+    if (fuse >= 2) TRY_CUDA(cudaMalloc(&L.mask, (size_t)mb * L.out));
+    TRY_CUDA(cudaEventCreateWithFlags(&L.dy_ready, cudaEventDisableTiming));
+    TRY_CUDA(cudaEventCreateWithFlags(&L.dw_ready, cudaEventDisableTiming));
+    TRY_CUDA(cudaEventCreateWithFlags(&L.updated, cudaEventDisableTiming));
+    TRY_CUDA(cudaEventCreateWithFlags(&L.dx_done, cudaEventDisableTiming));
+  }
+  *out = m;
+  return AINIC_OK;
+}
+
+extern "C" int ainic_mlp_destroy(ainic_mlp_t* m) {
+  if (!m) return AINIC_ERR_ARG;
+  cudaDeviceSynchronize();
+  for (auto& L : m->layers) {
+    cudaFree(L.wb); cudaFree(L.bias); cudaFree(L.dbias); cudaFree(L.mask);
+    cudaEventDestroy(L.dy_ready); cudaEventDestroy(L.dw_ready); cudaEventDestroy(L.updated); cudaEventDestroy(L.dx_done);
+  }
+  for (auto p : m->act) cudaFree(p);
+  for (auto p : m->dact) cudaFree(p);
+  cudaFree(m->loss_sum);
+  cudaEventDestroy(m->fwd_done);
+  cudaStreamDestroy(m->wgrad_stream);
+  cudaStreamDestroy(m->comm_stream);
+  delete m;
+  return AINIC_OK;
+}
+
+// Raw buffer access for initialisation, checkpointing and tests.
+// what: 0 weight fp32, 1 grad fp32, 2 shadow bf16, 3 bias fp32, 4 dbias fp32, 5 act bf16 (l in 0..L), 6 dact bf16 (1..L), 7 mask
+extern "C" void* ainic_mlp_buffer(ainic_mlp_t* m, int what, int l) {
+  if (!m || l < 0) return nullptr;
+  if (what == 5) return l <= m->nlayers ? m->act[l] : nullptr;
+  if (what == 6) return (l >= 1 && l <= m->nlayers) ? m->dact[l] : nullptr;
+  if (l >= m->nlayers) return nullptr;
+  Layer& L = m->layers[l];
+  switch (what) {
+    case 0: return L.w;
+    case 1: return L.g;
+    case 2: return L.wb;
+    case 3: return L.bias;
+    case 4: return L.dbias;
+    case 7: return L.mask;
+  }
+  return nullptr;
+}
+
+// Refresh every bf16 shadow from the fp32 masters (after init / checkpoint load).
+extern "C" int ainic_mlp_sync_shadows(ainic_mlp_t* m, void* stream) {
+  if (!m) return AINIC_ERR_ARG;
+  for (auto& L : m->layers) TRY(ainic_cast_f32_bf16(L.w, L.wb, (size_t)L.in * L.out, stream));
+  m->first_step = true;
+  return AINIC_OK;
+}
+
+extern "C" unsigned long long ainic_mlp_launches(ainic_mlp_t* m) { return m ? m->launches : 0; }
+extern "C" void* ainic_mlp_loss_ptr(ainic_mlp_t* m) { return m ? m->loss_sum : nullptr; }
+
+static int forward(ainic_mlp* m, cudaStream_t s, bool wait_updates) {
+  const bool use_bias = (m->fuse == 1 || m->fuse == 3), relu = (m->fuse >= 2);
+  for (int l = 0; l < m->nlayers; ++l) {
+    Layer& L = m->layers[l];
+    if (wait_updates && !m->first_step) TRY_CUDA(cudaStreamWaitEvent(s, L.updated, 0));
+    ainic_gemm_epilogue_t epi{};
+    epi.bias = use_bias ? L.bias : nullptr;
+    epi.relu = relu ? 1 : 0;
+    epi.mask_out = relu ? L.mask : nullptr;
+    epi.alpha = 1.0f;
+    TRY(ainic_gemm_bf16(AINIC_GEMM_NT, m->act[l], L.in, L.wb, L.in, m->act[l + 1], L.out, m->mb, L.out, L.in, &epi, 0,
+                        m->gemm_ctas, s));
+    m->launches++;
+  }
+  return AINIC_OK;
+}
+
+// Forward only: logits (bf16 [mb][C[L]]) stay in act[L].  x is copied/used in place as act[0].
+extern "C" int ainic_mlp_forward(ainic_mlp_t* m, const void* x_bf16, void* stream) {
+  if (!m || !x_bf16) return AINIC_ERR_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (x_bf16 != m->act[0])
+    TRY_CUDA(cudaMemcpyAsync(m->act[0], x_bf16, (size_t)m->mb * m->layers[0].in * 2, cudaMemcpyDeviceToDevice, s));
+  return forward(m, s, true);
+}
+
+// One full training iteration.  loss_out (device, nullable) receives the mean cross-entropy of this
+// rank's minibatch.  Returns after enqueueing; completion is stream/event ordered.
+extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t* labels, float* loss_out, void* stream) {
+  if (!m || !x_bf16 || !labels) return AINIC_ERR_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int Ln = m->nlayers;
+  const bool relu = (m->fuse >= 2), use_bias = (m->fuse == 1 || m->fuse == 3);
+  // act[0] is still being read by the previous step's last weight-gradient GEMM (wgrad stream is
+  // in order, so layer 0's event covers all of them).
+  if (!m->first_step) TRY_CUDA(cudaStreamWaitEvent(s, m->layers[0].dw_ready, 0));
+  if (x_bf16 != m->act[0])
+    TRY_CUDA(cudaMemcpyAsync(m->act[0], x_bf16, (size_t)m->mb * m->layers[0].in * 2, cudaMemcpyDeviceToDevice, s));
+  TRY(forward(m, s, true));
+  TRY_CUDA(cudaMemsetAsync(m->loss_sum, 0, 4, s));
+  TRY(ainic_softmax_xent(m->act[Ln], labels, nullptr, m->dact[Ln], m->loss_sum, m->mb, m->layers[Ln - 1].out,
+                         m->layers[Ln - 1].out, m->loss_weight, s));
+  m->launches++;
+  if (loss_out) TRY_CUDA(cudaMemcpyAsync(loss_out, m->loss_sum, 4, cudaMemcpyDeviceToDevice, s));
+  for (int l = Ln - 1; l >= 0; --l) {
+    Layer& L = m->layers[l];
+    // dact[l+1] is final here (for ReLU layers the mask was already applied by the producer below)
+    TRY_CUDA(cudaEventRecord(L.dy_ready, s));
+    // --- weight gradient on the wgrad stream: dW = dY^T . X -> flat fp32 bucket
+    TRY_CUDA(cudaStreamWaitEvent(m->wgrad_stream, L.dy_ready, 0));
+    ainic_gemm_epilogue_t we{};
+    we.alpha = 1.0f;
+    TRY(ainic_gemm_bf16(AINIC_GEMM_TN, m->dact[l + 1], L.out, m->act[l], L.in, L.g, L.in, L.out, L.in, m->mb, &we, 0,
+                        m->wgrad_ctas, m->wgrad_stream));
+    m->launches++;
+    if (use_bias) {
+      TRY(ainic_bias_grad(m->dact[l + 1], L.dbias, m->mb, L.out, L.out, m->wgrad_stream));
+      m->launches++;
+    }
+    TRY_CUDA(cudaEventRecord(L.dw_ready, m->wgrad_stream));
+    // --- data gradient on the main stream (critical path): dX = dY . W, masked by the previous ReLU
+    if (l > 0) {
+      ainic_gemm_epilogue_t de{};
+      de.alpha = 1.0f;
+      de.mask_in = relu ? m->layers[l - 1].mask : nullptr;
+      TRY(ainic_gemm_bf16(AINIC_GEMM_NN, m->dact[l + 1], L.out, L.wb, L.in, m->dact[l], L.in, m->mb, L.in, L.out, &de, 0,
+                          m->gemm_ctas, s));
+      m->launches++;
+      TRY_CUDA(cudaEventRecord(L.dx_done, s));
+    }
+    // --- fused all-reduce + SGD of bucket l on the comm stream
+    TRY_CUDA(cudaStreamWaitEvent(m->comm_stream, L.dw_ready, 0));
+    if (l > 0) TRY_CUDA(cudaStreamWaitEvent(m->comm_stream, L.dx_done, 0));  // shadow is rewritten below
+    ainic_allreduce_args_t a{};
+    a.grad = L.g;
+    a.weight = L.w;
+    a.weight_bf16 = L.wb;
+    a.count = (size_t)L.in * L.out;
+    a.lr = m->lr;
+    a.codec = m->codec;
+    a.bfp_mode = m->bfp_mode;
+    a.algo = m->algo;
+    a.max_ctas = m->comm_ctas;
+    TRY(ainic_allreduce_fused(m->comm, &a, m->comm_stream));
+    m->launches++;
+    TRY_CUDA(cudaEventRecord(L.updated, m->comm_stream));
+  }
+  m->first_step = false;
+  return AINIC_OK;
+}
+
+// Block the given stream until every outstanding weight update has landed (the reference's
+// wait(request[1]); wait(request[0]) at the end of an iteration, :775-787).
+extern "C" int ainic_mlp_wait_updates(ainic_mlp_t* m, void* stream) {
+  if (!m) return AINIC_ERR_ARG;
+  if (m->first_step) return AINIC_OK;
+  for (auto& L : m->layers) TRY_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, L.updated, 0));
+  return AINIC_OK;
+}

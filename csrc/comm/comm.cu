@@ -1,0 +1,327 @@
+// Communicator: symmetric heap over CUDA IPC + host-side dispatch of the fused all-reduce kernels.
+//
+// Replaces the reference's platform glue: DMA-able buffers from fpga.allocBuffer
+// (sw/mlp_mpi_example_f32.cpp:345-347, :396-401), MPF virtual addressing
+// (hw/cci_mpf_app_conf.vh:36-39) and the IKL ring routing of sw/setup_route.sh.  NVSwitch is
+// all-to-all, so "routing" is just mapping every peer's heap into this process.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+
+#include "allreduce.cuh"
+
+using namespace ainic;
+using namespace ainic::comm;
+
+static thread_local std::string g_last_error;
+static void set_error(const std::string& s) { g_last_error = s; }
+extern "C" const char* ainic_last_error(void) { return g_last_error.c_str(); }
+extern "C" const char* ainic_version(void) { return "b200-ainic 0.1 (sm_100a)"; }
+
+#define CUDA_TRY(expr)                                                                         \
+  do {                                                                                         \
+    cudaError_t _e = (expr);                                                                   \
+    if (_e != cudaSuccess) {                                                                   \
+      set_error(std::string(#expr) + ": " + cudaGetErrorString(_e));                           \
+      return AINIC_ERR_CUDA;                                                                   \
+    }                                                                                          \
+  } while (0)
+
+struct ainic_comm {
+  int rank = 0, nranks = 1, device = 0;
+  size_t heap_bytes = 0, bump = 0;
+  uint8_t* heap = nullptr;
+  uint8_t* peer_base[kMaxRanks] = {};
+  bool connected = false;
+  uint32_t* flags = nullptr;              // in heap
+  unsigned long long* counters = nullptr; // in heap
+  uint8_t* stage_c = nullptr;             // in heap, 2 halves
+  uint8_t* stage_d = nullptr;             // in heap
+  size_t stage_frames = 0;
+  uint32_t epoch = 0, parity = 0;
+  unsigned long long timeout_ns = 10ull * 1000 * 1000 * 1000;
+  volatile uint32_t* next_done_slot = nullptr;  // set by the NIC layer for the next launch
+};
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+// The ring inbox holds ceil(frames/(16N)) blocks x (2N-2) slices; rounding the block count up costs
+// at most one block = 14 raw slices of 32 KiB.
+static constexpr size_t kRingSlack = 512 * 1024;
+
+extern "C" int ainic_comm_create(ainic_comm_t** out, int rank, int nranks, size_t heap_bytes) {
+  if (!out || nranks < 1 || nranks > kMaxRanks || rank < 0 || rank >= nranks) return AINIC_ERR_ARG;
+  ainic_comm* c = new ainic_comm();
+  c->rank = rank;
+  c->nranks = nranks;
+  if (cudaGetDevice(&c->device) != cudaSuccess) { delete c; set_error("cudaGetDevice failed"); return AINIC_ERR_CUDA; }
+  const size_t reserved = align_up(kFlagWords * sizeof(uint32_t), 4096) + 4096;
+  c->heap_bytes = align_up(heap_bytes + reserved, 2u << 20);
+  cudaError_t e = cudaMalloc(&c->heap, c->heap_bytes);
+  if (e != cudaSuccess) { set_error(std::string("cudaMalloc heap: ") + cudaGetErrorString(e)); delete c; return AINIC_ERR_CUDA; }
+  cudaMemset(c->heap, 0, reserved);
+  cudaDeviceSynchronize();
+  c->flags = reinterpret_cast<uint32_t*>(c->heap);
+  c->counters = reinterpret_cast<unsigned long long*>(c->heap + align_up(kFlagWords * sizeof(uint32_t), 4096));
+  c->bump = reserved;
+  c->peer_base[rank] = c->heap;
+  c->connected = (nranks == 1);
+  if (const char* t = getenv("AINIC_TIMEOUT_MS")) c->timeout_ns = strtoull(t, nullptr, 10) * 1000000ull;
+  *out = c;
+  return AINIC_OK;
+}
+
+extern "C" int ainic_comm_export(ainic_comm_t* c, void* handle_out) {
+  if (!c || !handle_out) return AINIC_ERR_ARG;
+  static_assert(sizeof(cudaIpcMemHandle_t) == AINIC_IPC_HANDLE_BYTES, "IPC handle size");
+  cudaIpcMemHandle_t h;
+  CUDA_TRY(cudaIpcGetMemHandle(&h, c->heap));
+  memcpy(handle_out, &h, sizeof(h));
+  return AINIC_OK;
+}
+
+extern "C" int ainic_comm_connect(ainic_comm_t* c, const void* all_handles) {
+  if (!c || (!all_handles && c->nranks > 1)) return AINIC_ERR_ARG;
+  for (int p = 0; p < c->nranks; ++p) {
+    if (p == c->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, static_cast<const uint8_t*>(all_handles) + (size_t)p * sizeof(h), sizeof(h));
+    void* ptr = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    c->peer_base[p] = static_cast<uint8_t*>(ptr);
+  }
+  c->connected = true;
+  return AINIC_OK;
+}
+
+extern "C" int ainic_comm_destroy(ainic_comm_t* c) {
+  if (!c) return AINIC_ERR_ARG;
+  cudaDeviceSynchronize();
+  for (int p = 0; p < c->nranks; ++p)
+    if (p != c->rank && c->peer_base[p]) cudaIpcCloseMemHandle(c->peer_base[p]);
+  if (c->heap) cudaFree(c->heap);
+  delete c;
+  return AINIC_OK;
+}
+
+extern "C" void* ainic_comm_alloc(ainic_comm_t* c, size_t bytes, size_t align) {
+  if (!c || bytes == 0) return nullptr;
+  if (align < 256) align = 256;
+  const size_t off = align_up(c->bump, align);
+  if (off + bytes > c->heap_bytes) { set_error("symmetric heap exhausted"); return nullptr; }
+  c->bump = off + bytes;
+  return c->heap + off;
+}
+
+extern "C" void* ainic_comm_peer_ptr(ainic_comm_t* c, const void* local_ptr, int peer) {
+  if (!c || peer < 0 || peer >= c->nranks || !c->peer_base[peer]) return nullptr;
+  const uint8_t* p = static_cast<const uint8_t*>(local_ptr);
+  if (p < c->heap || p >= c->heap + c->heap_bytes) return nullptr;
+  return c->peer_base[peer] + (p - c->heap);
+}
+extern "C" int ainic_comm_rank(const ainic_comm_t* c) { return c ? c->rank : -1; }
+extern "C" int ainic_comm_size(const ainic_comm_t* c) { return c ? c->nranks : -1; }
+
+extern "C" int ainic_comm_counters(ainic_comm_t* c, uint64_t out[8]) {
+  if (!c || !out) return AINIC_ERR_ARG;
+  CUDA_TRY(cudaMemcpy(out, c->counters, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  return AINIC_OK;
+}
+
+// Internal hooks for the NIC layer (api/nic.cu).
+extern "C" void ainic_comm_set_done_slot_(ainic_comm_t* c, volatile uint32_t* dev_visible_slot) { c->next_done_slot = dev_visible_slot; }
+extern "C" void ainic_comm_set_timeout_ns_(ainic_comm_t* c, unsigned long long ns) { c->timeout_ns = ns; }
+
+// ---------------------------------------------------------------------------------------- dispatch
+typedef void (*KernFn)(const RankCtx);
+typedef void (*EmulFn)(const RankCtx*);
+
+template <int ALGO>
+static KernFn pick_kernel(int codec, int mode) {
+  switch (codec) {
+    case AINIC_CODEC_F32: return allreduce_kernel<ALGO, 0, 0>;
+    case AINIC_CODEC_BFP: return mode == AINIC_BFP_HW_EXACT ? allreduce_kernel<ALGO, 1, 0> : allreduce_kernel<ALGO, 1, 1>;
+    case AINIC_CODEC_MXFP8: return allreduce_kernel<ALGO, 2, 0>;
+    case AINIC_CODEC_BF16: return allreduce_kernel<ALGO, 3, 0>;
+  }
+  return nullptr;
+}
+template <int ALGO>
+static EmulFn pick_emul(int codec, int mode) {
+  switch (codec) {
+    case AINIC_CODEC_F32: return allreduce_emul_kernel<ALGO, 0, 0>;
+    case AINIC_CODEC_BFP: return mode == AINIC_BFP_HW_EXACT ? allreduce_emul_kernel<ALGO, 1, 0> : allreduce_emul_kernel<ALGO, 1, 1>;
+    case AINIC_CODEC_MXFP8: return allreduce_emul_kernel<ALGO, 2, 0>;
+    case AINIC_CODEC_BF16: return allreduce_emul_kernel<ALGO, 3, 0>;
+  }
+  return nullptr;
+}
+static KernFn pick_kernel(int algo, int codec, int mode) {
+  switch (algo) {
+    case AINIC_ALGO_ONESHOT: return pick_kernel<AINIC_ALGO_ONESHOT>(codec, mode);
+    case AINIC_ALGO_TWOSHOT: return pick_kernel<AINIC_ALGO_TWOSHOT>(codec, mode);
+    case AINIC_ALGO_RING: return (codec == AINIC_CODEC_F32 || codec == AINIC_CODEC_BFP) ? pick_kernel<AINIC_ALGO_RING>(codec, mode) : nullptr;
+  }
+  return nullptr;
+}
+static EmulFn pick_emul(int algo, int codec, int mode) {
+  switch (algo) {
+    case AINIC_ALGO_ONESHOT: return pick_emul<AINIC_ALGO_ONESHOT>(codec, mode);
+    case AINIC_ALGO_TWOSHOT: return pick_emul<AINIC_ALGO_TWOSHOT>(codec, mode);
+    case AINIC_ALGO_RING: return (codec == AINIC_CODEC_F32 || codec == AINIC_CODEC_BFP) ? pick_emul<AINIC_ALGO_RING>(codec, mode) : nullptr;
+  }
+  return nullptr;
+}
+
+static int resolve_algo(int algo, int nranks, size_t count) {
+  if (algo != AINIC_ALGO_AUTO) return algo;
+  if (nranks == 1) return AINIC_ALGO_ONESHOT;
+  return count * sizeof(float) <= (512u << 10) ? AINIC_ALGO_ONESHOT : AINIC_ALGO_TWOSHOT;
+}
+
+// How many CTAs a call uses.  Enough warps to keep ~2 MB in flight over NVLink, few enough to leave
+// most SMs to the concurrent backward GEMMs.
+static int default_ctas(int algo, int nranks, size_t count) {
+  const size_t frames = bfp_frames(count);
+  size_t work = frames;  // frames per rank per phase
+  if (algo == AINIC_ALGO_RING) work = (frames + (size_t)nranks * kSliceFrames - 1) / ((size_t)nranks * kSliceFrames);
+  else work = (frames + 15) / 16;  // 16 warps per CTA, one frame each
+  size_t ctas = work < 1 ? 1 : work;
+  const size_t cap = 64;
+  if (ctas > cap) ctas = cap;
+  return (int)ctas;
+}
+
+static int check_ring_limits(int nranks, size_t count, int ctas) {
+  const size_t frames = bfp_frames(count);
+  const size_t nblocks = (frames + (size_t)nranks * kSliceFrames - 1) / ((size_t)nranks * kSliceFrames);
+  const size_t per_cta = (nblocks + ctas - 1) / ctas;
+  return per_cta * (2 * nranks - 2) < 4096 ? AINIC_OK : AINIC_ERR_ARG;
+}
+
+static int ensure_staging(ainic_comm* c, size_t count) {
+  const size_t frames = bfp_frames(count);
+  if (frames <= c->stage_frames) return AINIC_OK;
+  // Grow-only; every rank sees the same call sequence, so offsets stay symmetric.
+  const size_t want = frames;
+  uint8_t* sc = static_cast<uint8_t*>(ainic_comm_alloc(c, 2 * want * 1024, 4096));
+  uint8_t* sd = static_cast<uint8_t*>(ainic_comm_alloc(c, 2 * want * 2048 + kRingSlack, 4096));
+  if (!sc || !sd) return AINIC_ERR_ARG;
+  c->stage_c = sc;
+  c->stage_d = sd;
+  c->stage_frames = want;
+  return AINIC_OK;
+}
+
+extern "C" int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args_t* a, void* stream) {
+  if (!c || !a || !a->grad || a->count == 0) return AINIC_ERR_ARG;
+  if (!c->connected) { set_error("communicator not connected"); return AINIC_ERR_ARG; }
+  if (((uintptr_t)a->grad & 15) || ((uintptr_t)a->weight & 15) || ((uintptr_t)a->weight_bf16 & 7) || ((uintptr_t)a->grad_out & 15))
+    return AINIC_ERR_ARG;
+  const int algo = resolve_algo(a->algo, c->nranks, a->count);
+  KernFn kern = pick_kernel(algo, a->codec, a->bfp_mode);
+  if (!kern) { set_error("unsupported algo/codec combination"); return AINIC_ERR_UNSUPPORTED; }
+  if (c->nranks > 1 && !ainic_comm_peer_ptr(c, a->grad, 0) && a->codec == AINIC_CODEC_F32) {
+    set_error("fp32 (in-place) all-reduce needs the gradient bucket inside the symmetric heap");
+    return AINIC_ERR_ARG;
+  }
+  int rc = ensure_staging(c, a->count);
+  if (rc) return rc;
+  int ctas = a->max_ctas > 0 ? a->max_ctas : default_ctas(algo, c->nranks, a->count);
+  if (ctas > kMaxCtas) ctas = kMaxCtas;
+  if (algo == AINIC_ALGO_RING && check_ring_limits(c->nranks, a->count, ctas)) { set_error("ring: too many blocks per CTA"); return AINIC_ERR_ARG; }
+
+  RankCtx ctx{};
+  ctx.rank = c->rank;
+  ctx.nranks = c->nranks;
+  ctx.grad = a->grad;
+  ctx.weight = a->weight;
+  ctx.wshadow = static_cast<__nv_bfloat16*>(a->weight_bf16);
+  ctx.grad_out = a->grad_out;
+  for (int p = 0; p < c->nranks; ++p) {
+    ctx.peer_grad[p] = p == c->rank ? a->grad : static_cast<const float*>(ainic_comm_peer_ptr(c, a->grad, p));
+    ctx.stage_c[p] = c->peer_base[p] + (c->stage_c - c->heap);
+    ctx.stage_d[p] = c->peer_base[p] + (c->stage_d - c->heap);
+    ctx.flags[p] = reinterpret_cast<uint32_t*>(c->peer_base[p]);
+  }
+  ctx.counters = c->counters;
+  ctx.done_slot = c->next_done_slot;
+  c->next_done_slot = nullptr;
+  ctx.count = a->count;
+  ctx.stage_c_half = c->stage_frames * 1024;
+  ctx.lr = a->lr;
+  ctx.epoch = ++c->epoch;
+  ctx.parity = (c->parity ^= 1u);
+  ctx.timeout_ns = c->timeout_ns;
+  kern<<<ctas, kCommThreads, 0, (cudaStream_t)stream>>>(ctx);
+  CUDA_TRY(cudaGetLastError());
+  return AINIC_OK;
+}
+
+// ---------------------------------------------------------------------------------------- emulation
+extern "C" int ainic_allreduce_emulate(int nranks, float* grads, float* weights, void* weights_bf16, float* grads_out,
+                                       size_t count, float lr, int codec, int bfp_mode, int algo, int ctas_per_rank,
+                                       void* stream) {
+  if (nranks < 1 || nranks > kMaxRanks || !grads || count == 0) return AINIC_ERR_ARG;
+  algo = resolve_algo(algo, nranks, count);
+  EmulFn kern = pick_emul(algo, codec, bfp_mode);
+  if (!kern) return AINIC_ERR_UNSUPPORTED;
+  int ctas = ctas_per_rank > 0 ? ctas_per_rank : 4;
+  if (algo == AINIC_ALGO_RING && check_ring_limits(nranks, count, ctas)) return AINIC_ERR_ARG;
+  int dev = 0, sms = 0, per_sm = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kCommThreads, 0));
+  if ((long)ctas * nranks > (long)sms * per_sm) { set_error("emulation grid exceeds co-resident capacity"); return AINIC_ERR_ARG; }
+
+  const size_t frames = bfp_frames(count);
+  const size_t c_bytes = 2 * frames * 1024, d_bytes = 2 * frames * 2048 + kRingSlack;
+  const size_t flag_bytes = kFlagWords * sizeof(uint32_t), ctr_bytes = 64;
+  const size_t per_rank = align_up(c_bytes, 256) + align_up(d_bytes, 256) + flag_bytes + ctr_bytes;
+  uint8_t* scratch = nullptr;
+  RankCtx* d_ctx = nullptr;
+  CUDA_TRY(cudaMalloc(&scratch, per_rank * nranks));
+  CUDA_TRY(cudaMalloc(&d_ctx, sizeof(RankCtx) * nranks));
+  cudaStream_t s = (cudaStream_t)stream;
+  CUDA_TRY(cudaMemsetAsync(scratch, 0, per_rank * nranks, s));
+  RankCtx h[kMaxRanks];
+  memset(h, 0, sizeof(h));
+  auto base = [&](int r) { return scratch + (size_t)r * per_rank; };
+  for (int r = 0; r < nranks; ++r) {
+    RankCtx& x = h[r];
+    x.rank = r;
+    x.nranks = nranks;
+    x.grad = grads + (size_t)r * count;
+    x.weight = weights ? weights + (size_t)r * count : nullptr;
+    x.wshadow = weights_bf16 ? static_cast<__nv_bfloat16*>(weights_bf16) + (size_t)r * count : nullptr;
+    x.grad_out = grads_out ? grads_out + (size_t)r * count : nullptr;
+    for (int p = 0; p < nranks; ++p) {
+      x.peer_grad[p] = grads + (size_t)p * count;
+      x.stage_c[p] = base(p);
+      x.stage_d[p] = base(p) + align_up(c_bytes, 256);
+      x.flags[p] = reinterpret_cast<uint32_t*>(base(p) + align_up(c_bytes, 256) + align_up(d_bytes, 256));
+    }
+    x.counters = reinterpret_cast<unsigned long long*>(base(r) + align_up(c_bytes, 256) + align_up(d_bytes, 256) + flag_bytes);
+    x.done_slot = nullptr;
+    x.count = count;
+    x.stage_c_half = frames * 1024;
+    x.lr = lr;
+    x.epoch = 1;
+    x.parity = 0;
+    x.timeout_ns = 5ull * 1000 * 1000 * 1000;
+  }
+  CUDA_TRY(cudaMemcpyAsync(d_ctx, h, sizeof(RankCtx) * nranks, cudaMemcpyHostToDevice, s));
+  const RankCtx* arg0 = d_ctx;
+  void* args[] = {(void*)&arg0};
+  cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas, nranks), dim3(kCommThreads), args, 0, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  unsigned long long ctr[8] = {};
+  if (e == cudaSuccess) cudaMemcpy(ctr, h[0].counters, sizeof(ctr), cudaMemcpyDeviceToHost);
+  cudaFree(scratch);
+  cudaFree(d_ctx);
+  if (e != cudaSuccess) { set_error(std::string("emulate: ") + cudaGetErrorString(e)); return AINIC_ERR_CUDA; }
+  if (ctr[CTR_TIMEOUTS]) { set_error("emulate: flag wait timed out"); return AINIC_ERR_TIMEOUT; }
+  return AINIC_OK;
+}

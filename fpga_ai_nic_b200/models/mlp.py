@@ -1,0 +1,159 @@
+"""The reference's MLP (sw/mlp_mpi_example_f32.cpp) on B200.
+
+``MLPTrainer`` drives the native executor ``ainic_mlp_*`` (csrc/api/mlp.cu): tcgen05 GEMMs for the
+fully-connected layers, a fused softmax/cross-entropy kernel, and one fused all-reduce + SGD kernel
+per layer bucket, overlapped with the rest of the backward pass.  ``MLPConfig.reference()`` is the
+reference run (10 x 2048 x 2048, 1792 samples per rank, fuse 0; sw/run.sh:16).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import torch
+
+from .. import _native as N
+from ..ops import kernels as K
+from ..ops import oracle as O
+from ..parallel.comm import Communicator, tensor_from_ptr
+
+
+@dataclass
+class MLPConfig:
+    sizes: list = field(default_factory=lambda: [2048] * 11)   # C[0..L]
+    mb: int = 1792                                             # samples per rank
+    fuse: int = 0                                              # 0 none, 1 bias, 2 relu, 3 bias+relu
+    lr: float = 0.1                                            # hw/weight_update.sv:439-444 (-0.1)
+    loss_weight: float = 0.1                                   # sw/mlp_mpi_example_f32.cpp:250
+    codec: str = "auto"                                        # auto: f32 on 1 rank, bfp otherwise
+    bfp_mode: int = K.CLEAN
+    algo: str = "auto"
+    seed: int = 1                                              # libxsmm_rng_set_seed(1), :273
+
+    @staticmethod
+    def reference(nlayers: int = 10, width: int = 2048, mb: int = 1792) -> "MLPConfig":
+        return MLPConfig(sizes=[width] * (nlayers + 1), mb=mb)
+
+    @property
+    def nlayers(self) -> int:
+        return len(self.sizes) - 1
+
+    def flops_per_step(self, global_mb: int) -> float:
+        """The reference's accounting: 6*MB*C*K per layer, 4* for layer 0 (:794-798)."""
+        f = 0.0
+        for l in range(self.nlayers):
+            f += (4.0 if l == 0 else 6.0) * global_mb * self.sizes[l] * self.sizes[l + 1]
+        return f
+
+    def param_count(self) -> int:
+        return sum(self.sizes[l] * self.sizes[l + 1] for l in range(self.nlayers))
+
+    def heap_bytes(self) -> int:
+        p = self.param_count()
+        biggest = max(self.sizes[l] * self.sizes[l + 1] for l in range(self.nlayers))
+        frames = (biggest + 511) // 512
+        return p * 8 + frames * (2 * 1024 + 2 * 2048) + (8 << 20) + self.nlayers * 16384
+
+
+class MLPTrainer:
+    def __init__(self, cfg: MLPConfig, comm: Communicator | None = None):
+        self.cfg = cfg
+        self.lib = N.cuda()
+        self.comm = comm if comm is not None else Communicator(cfg.heap_bytes())
+        self.world = self.comm.world_size
+        codec = cfg.codec
+        if codec == "auto":
+            codec = "f32" if self.world == 1 else "bfp"   # nothing crosses a wire on one rank
+        self.codec = K.CODEC_NAMES[codec]
+        self.algo = K.ALGO_NAMES[cfg.algo]
+        sizes = (C.c_int * len(cfg.sizes))(*cfg.sizes)
+        h = C.c_void_p()
+        N.check(self.lib.ainic_mlp_create(C.byref(h), self.comm.handle, cfg.nlayers, sizes, cfg.mb, cfg.fuse, cfg.lr,
+                                          cfg.loss_weight, self.codec, cfg.bfp_mode, self.algo), "mlp_create")
+        self.handle = h
+        self.device = self.comm.device
+        self.loss_dev = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self._views: dict = {}
+        self.init_weights()
+
+    # -- buffers ------------------------------------------------------------------------------
+    _WHAT = {"weight": (0, torch.float32), "grad": (1, torch.float32), "shadow": (2, torch.bfloat16),
+             "bias": (3, torch.float32), "dbias": (4, torch.float32), "act": (5, torch.bfloat16),
+             "dact": (6, torch.bfloat16), "mask": (7, torch.uint8)}
+
+    def buffer(self, what: str, layer: int) -> torch.Tensor:
+        key = (what, layer)
+        if key not in self._views:
+            code, dt = self._WHAT[what]
+            ptr = self.lib.ainic_mlp_buffer(self.handle, code, layer)
+            if not ptr:
+                raise KeyError(key)
+            s = self.cfg.sizes
+            if what in ("weight", "grad", "shadow"):
+                shape = (s[layer + 1], s[layer])
+            elif what in ("bias", "dbias"):
+                shape = (s[layer + 1],)
+            elif what == "mask":
+                shape = (self.cfg.mb, s[layer + 1])
+            else:
+                shape = (self.cfg.mb, s[layer])
+            self._views[key] = tensor_from_ptr(ptr, shape, dt, owner=self, device=self.device)
+        return self._views[key]
+
+    def init_weights(self) -> None:
+        """0.05 - U[0,1)/10 per buffer (sw/mlp_mpi_example_f32.cpp:182-189, :415-450).  Every rank
+        uses the same seed, which is what rank 0's MPI_Bcast achieves in the reference (:463-470)."""
+        for l in range(self.cfg.nlayers):
+            w = self.buffer("weight", l)
+            w.copy_(O.init_buf(w.numel(), seed=self.cfg.seed * 1000 + l).view_as(w))
+            self.buffer("bias", l).copy_(O.init_buf(self.cfg.sizes[l + 1], seed=self.cfg.seed * 1000 + 500 + l))
+        self.sync_shadows()
+
+    def sync_shadows(self) -> None:
+        N.check(self.lib.ainic_mlp_sync_shadows(self.handle, N.stream_ptr()), "mlp_sync_shadows")
+        torch.cuda.current_stream().synchronize()
+
+    # -- execution ------------------------------------------------------------------------------
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        assert x.dtype == torch.bfloat16 and x.is_cuda and x.is_contiguous()
+        N.check(self.lib.ainic_mlp_forward(self.handle, x.data_ptr(), N.stream_ptr()), "mlp_forward")
+        return self.buffer("act", self.cfg.nlayers)
+
+    def step(self, x: torch.Tensor, labels: torch.Tensor, want_loss: bool = True) -> torch.Tensor | None:
+        """One training iteration (enqueue only).  Returns the device scalar holding this rank's
+        summed cross-entropy (divide by mb for the mean)."""
+        assert x.dtype == torch.bfloat16 and x.is_cuda and x.is_contiguous()
+        assert labels.dtype == torch.int32 and labels.is_cuda
+        N.check(self.lib.ainic_mlp_step(self.handle, x.data_ptr(), labels.data_ptr(),
+                                        self.loss_dev.data_ptr() if want_loss else None, N.stream_ptr()), "mlp_step")
+        return self.loss_dev if want_loss else None
+
+    def wait(self) -> None:
+        """Make the current stream wait for all outstanding weight updates (reference: wait(), :157-180)."""
+        N.check(self.lib.ainic_mlp_wait_updates(self.handle, N.stream_ptr()), "mlp_wait_updates")
+
+    @property
+    def launches(self) -> int:
+        return int(self.lib.ainic_mlp_launches(self.handle))
+
+    # -- checkpoint / resume (the reference has none: SURVEY section 5) ---------------------------
+    def state_dict(self) -> dict:
+        self.wait()
+        torch.cuda.synchronize()
+        return {"sizes": list(self.cfg.sizes),
+                "weights": [self.buffer("weight", l).cpu().clone() for l in range(self.cfg.nlayers)],
+                "biases": [self.buffer("bias", l).cpu().clone() for l in range(self.cfg.nlayers)]}
+
+    def load_state_dict(self, sd: dict) -> None:
+        assert list(sd["sizes"]) == list(self.cfg.sizes)
+        self.wait()
+        torch.cuda.synchronize()
+        for l in range(self.cfg.nlayers):
+            self.buffer("weight", l).copy_(sd["weights"][l])
+            self.buffer("bias", l).copy_(sd["biases"][l])
+        self.sync_shadows()
+
+    def close(self) -> None:
+        if self.handle:
+            self.lib.ainic_mlp_destroy(self.handle)
+            self.handle = None

@@ -1,0 +1,108 @@
+"""Communicator: one symmetric heap per GPU, mapped into every peer over CUDA IPC.
+
+Role in the reference: OPAE buffer allocation + MPF address translation + the IKL ring routing
+script (sw/mlp_mpi_example_f32.cpp:304-350, hw/cci_mpf_app_conf.vh, sw/setup_route.sh).  Here
+torch.distributed is only the rendezvous (it carries 64-byte IPC handles once); all gradient
+traffic afterwards is peer loads/stores issued by our own kernels over NVLink.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+from .. import _native as N
+from ..ops import kernels as K
+
+_DT_CODES = {torch.float32: "<f4", torch.bfloat16: "<u2", torch.uint8: "|u1", torch.int32: "<i4", torch.uint32: "<u4"}
+
+
+class _CudaBlob:
+    """Minimal __cuda_array_interface__ carrier so torch can view native memory without a copy."""
+
+    def __init__(self, ptr: int, nbytes: int, owner):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+        self._owner = owner
+
+
+def tensor_from_ptr(ptr: int, shape, dtype: torch.dtype, owner=None, device=None) -> torch.Tensor:
+    nbytes = int(torch.tensor([], dtype=dtype).element_size())
+    for s in shape:
+        nbytes *= int(s)
+    dev = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+    raw = torch.as_tensor(_CudaBlob(ptr, nbytes, owner), device=dev)
+    return raw.view(dtype).view(*shape)
+
+
+class Communicator:
+    def __init__(self, heap_bytes: int, rank: int | None = None, world_size: int | None = None, group=None):
+        import torch.distributed as dist
+        self.lib = N.cuda()
+        if world_size is None:
+            world_size = dist.get_world_size(group) if dist.is_initialized() else 1
+        if rank is None:
+            rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.rank, self.world_size = rank, world_size
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        h = C.c_void_p()
+        N.check(self.lib.ainic_comm_create(C.byref(h), rank, world_size, heap_bytes), "comm_create")
+        self.handle = h
+        if world_size > 1:
+            buf = (C.c_uint8 * 64)()
+            N.check(self.lib.ainic_comm_export(self.handle, buf), "comm_export")
+            mine = bytes(buf)
+            gathered: list = [None] * world_size
+            dist.all_gather_object(gathered, mine, group=group)
+            blob = b"".join(gathered)
+            N.check(self.lib.ainic_comm_connect(self.handle, blob), "comm_connect")
+            dist.barrier(group=group)
+        self._closed = False
+
+    # -- symmetric allocations -------------------------------------------------------------
+    def alloc_ptr(self, nbytes: int, align: int = 4096) -> int:
+        p = self.lib.ainic_comm_alloc(self.handle, nbytes, align)
+        if not p:
+            raise N.NativeError("symmetric heap exhausted: " + self.lib.ainic_last_error().decode())
+        return p
+
+    def empty(self, shape, dtype=torch.float32) -> torch.Tensor:
+        """A tensor inside the symmetric heap.  Every rank must allocate in the same order."""
+        if isinstance(shape, int):
+            shape = (shape,)
+        nbytes = torch.tensor([], dtype=dtype).element_size()
+        for s in shape:
+            nbytes *= int(s)
+        return tensor_from_ptr(self.alloc_ptr(nbytes), shape, dtype, owner=self, device=self.device)
+
+    def peer_ptr(self, t: torch.Tensor, peer: int) -> int:
+        return self.lib.ainic_comm_peer_ptr(self.handle, t.data_ptr(), peer)
+
+    # -- fused all-reduce (+ SGD) -----------------------------------------------------------
+    def allreduce_fused(self, grad: torch.Tensor, weight: torch.Tensor | None = None, lr: float = 0.0,
+                        weight_bf16: torch.Tensor | None = None, grad_out: torch.Tensor | None = None,
+                        codec: int = K.CODEC_BFP, bfp_mode: int = K.CLEAN, algo: int = K.ALGO_AUTO, max_ctas: int = 0,
+                        stream=None) -> None:
+        a = N.AllreduceArgs(grad.data_ptr(), weight.data_ptr() if weight is not None else None,
+                            weight_bf16.data_ptr() if weight_bf16 is not None else None,
+                            grad_out.data_ptr() if grad_out is not None else None, grad.numel(), lr, codec, bfp_mode,
+                            algo, max_ctas)
+        N.check(self.lib.ainic_allreduce_fused(self.handle, C.byref(a), N.stream_ptr(stream)), "allreduce_fused")
+        K._count()
+
+    def counters(self) -> dict:
+        out = (C.c_uint64 * 8)()
+        N.check(self.lib.ainic_comm_counters(self.handle, out), "comm_counters")
+        return {"busy_ns": out[0], "wait_ns": out[1], "launches": out[2], "timeouts": out[3], "last_ns": out[5]}
+
+    def close(self) -> None:
+        if not self._closed:
+            self._closed = True
+            self.lib.ainic_comm_destroy(self.handle)
+
+    def __del__(self):  # best effort; explicit close() preferred
+        try:
+            if not self._closed and os.environ.get("AINIC_NO_DEL_CLOSE") is None:
+                self.close()
+        except Exception:
+            pass

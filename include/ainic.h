@@ -1,0 +1,183 @@
+/* b200-ainic public C API.
+ *
+ * Everything the reference exposes through its host driver functions
+ * (sw/mlp_mpi_example_f32.cpp:35-180: ikl_setup / all_reduce_setup / all_reduce / wait /
+ * get_all_reduce_latency / get_host_stall_cycles) plus the kernels the FPGA datapath and the
+ * libxsmm_dnn calls turn into on a B200.  All entry points are extern "C", take raw device
+ * pointers and a cudaStream_t passed as void*, and return AINIC_OK (0) or a negative error.
+ */
+#ifndef AINIC_H_
+#define AINIC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AINIC_OK 0
+#define AINIC_ERR_ARG (-1)
+#define AINIC_ERR_CUDA (-2)
+#define AINIC_ERR_TIMEOUT (-3)
+#define AINIC_ERR_BUSY (-4)
+#define AINIC_ERR_ABORTED (-5)
+#define AINIC_ERR_UNSUPPORTED (-6)
+
+#define AINIC_MAX_RANKS 8
+#define AINIC_DONE_SLOTS 8 /* hw/all_reduce.sv:1228 3-bit done_id; sw/mlp_mpi_example_f32.cpp:115-118 */
+
+/* gradient wire formats */
+#define AINIC_CODEC_F32 0
+#define AINIC_CODEC_BFP 1  /* reference BFP16x8: hw/bfp_adapter.sv */
+#define AINIC_CODEC_MXFP8 2
+#define AINIC_CODEC_BF16 3
+/* BFP numerics */
+#define AINIC_BFP_HW_EXACT 0
+#define AINIC_BFP_CLEAN 1
+/* all-reduce algorithms */
+#define AINIC_ALGO_AUTO 0
+#define AINIC_ALGO_ONESHOT 1
+#define AINIC_ALGO_TWOSHOT 2
+#define AINIC_ALGO_RING 3 /* reference-faithful schedule, hw/all_reduce.sv:686-1088 */
+#define AINIC_ALGO_NVLS 4
+
+const char* ainic_version(void);
+const char* ainic_last_error(void);
+
+/* ---------------------------------------------------------------- codecs (K8/K8', K14) */
+size_t ainic_bfp_bytes(size_t count);
+size_t ainic_mx_bytes(size_t count);
+int ainic_bfp_compress(const float* x, size_t count, uint8_t* out, int mode, void* stream);
+int ainic_bfp_decompress(const uint8_t* in, size_t count, float* out, int mode, void* stream);
+int ainic_mx_compress(const float* x, size_t count, uint8_t* out, void* stream);
+int ainic_mx_decompress(const uint8_t* in, size_t count, float* out, void* stream);
+
+/* ---------------------------------------------------------------- fused SGD (K9, hw/weight_update.sv:440-452)
+ * w = fmaf(-lr, g, w); optional bf16 shadow of the new weights for the tensor-core GEMMs. */
+int ainic_sgd(float* w, const float* g, void* w_bf16 /*nullable*/, size_t count, float lr, void* stream);
+int ainic_cast_f32_bf16(const float* x, void* y_bf16, size_t count, void* stream);
+
+/* ---------------------------------------------------------------- MLP kernels (K1-K5) */
+#define AINIC_GEMM_NT 0 /* C[M,N] = A[M,K] . B[N,K]^T  bf16 out  (forward)        */
+#define AINIC_GEMM_NN 1 /* C[M,N] = A[M,K] . B[K,N]    bf16 out  (backward data)  */
+#define AINIC_GEMM_TN 2 /* C[M,N] = A[K,M]^T . B[K,N]  fp32 out  (backward weight)*/
+typedef struct ainic_gemm_epilogue {
+  const float* bias;      /* [N], added before activation (bf16 outputs) */
+  uint8_t* mask_out;      /* [M][ldc] ReLU mask written by the forward pass */
+  const uint8_t* mask_in; /* [M][ldc] ReLU mask applied by the backward-data pass */
+  float alpha;            /* fp32 outputs: scale */
+  int relu;
+  int accumulate;         /* fp32 outputs: C += result */
+} ainic_gemm_epilogue_t;
+/* bf16 operands, fp32 accumulation on tcgen05 tensor cores.  block_n = 0 picks the tile width,
+ * max_ctas = 0 uses every SM (a smaller value leaves SMs for a concurrent all-reduce kernel). */
+int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b, int ldb, void* c, int ldc, int M, int N,
+                    int K, const ainic_gemm_epilogue_t* epi, int block_n, int max_ctas, void* stream);
+
+/* Row softmax + cross-entropy; dlogits = loss_weight*(p - onehot)/mb as bf16; loss_sum += sum_i CE_i.
+ * (libxsmm_dnn_smax_{fwd,bwd}_exec_f32, sw/mlp_mpi_example_f32.cpp:718-728) */
+int ainic_softmax_xent(const void* logits_bf16, const int32_t* labels, void* probs_bf16 /*nullable*/,
+                       void* dlogits_bf16, float* loss_sum, int mb, int n, int ld, float loss_weight, void* stream);
+/* dbias[n] = sum over rows of dy[mb][n] (bf16 in, fp32 out) */
+int ainic_bias_grad(const void* dy_bf16, float* dbias, int mb, int n, int ld, void* stream);
+
+/* ---------------------------------------------------------------- communicator (C1, C14, C21)
+ * One communicator per process/GPU.  The symmetric heap is one device allocation per rank whose
+ * IPC handle is exchanged by the caller (torch.distributed store, files, MPI ...): create ->
+ * export handle -> all-gather handles out of band -> connect.  nranks == 1 needs no exchange. */
+typedef struct ainic_comm ainic_comm_t;
+#define AINIC_IPC_HANDLE_BYTES 64
+int ainic_comm_create(ainic_comm_t** out, int rank, int nranks, size_t heap_bytes);
+int ainic_comm_export(ainic_comm_t* c, void* handle_out /*64 B*/);
+int ainic_comm_connect(ainic_comm_t* c, const void* all_handles /*nranks*64 B, rank order*/);
+int ainic_comm_destroy(ainic_comm_t* c);
+/* Bump allocator inside the symmetric heap; every rank must allocate in the same order so that
+ * offsets match (the reference's flat DMA-able buffers from fpga.allocBuffer,
+ * sw/mlp_mpi_example_f32.cpp:396-401). */
+void* ainic_comm_alloc(ainic_comm_t* c, size_t bytes, size_t align);
+void* ainic_comm_peer_ptr(ainic_comm_t* c, const void* local_ptr, int peer);
+int ainic_comm_rank(const ainic_comm_t* c);
+int ainic_comm_size(const ainic_comm_t* c);
+
+typedef struct ainic_allreduce_args {
+  float* grad;        /* flat fp32 gradient bucket inside the symmetric heap (sum of all ranks on return
+                         only for algo RING/f32 paths; compressed paths leave it untouched) */
+  float* weight;      /* flat fp32 master weights, updated in place: w -= lr * sum(g)   (nullable) */
+  void* weight_bf16;  /* bf16 shadow of the updated weights (nullable) */
+  float* grad_out;    /* where to write the reduced gradient when no weight update is fused (nullable) */
+  size_t count;       /* values */
+  float lr;
+  int codec, bfp_mode, algo;
+  int max_ctas;       /* 0 = default */
+} ainic_allreduce_args_t;
+/* Fused compress -> (peer pull) -> fp32 reduce -> decompress -> SGD, one kernel launch on stream. */
+int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args_t* args, void* stream);
+/* Device-side phase counters of the last completed fused all-reduce (ns from %globaltimer):
+ * [0] total busy, [1] waiting for peers, [2] launches.  The analogue of lpbk_latency /
+ * stall_* (hw/all_reduce.sv:92-98, :892-1072). */
+int ainic_comm_counters(ainic_comm_t* c, uint64_t out[8]);
+
+/* Single-GPU emulation of an N-rank all-reduce: all ranks' buffers live on one device and one
+ * cooperative launch runs every rank's CTAs (the software analogue of the withheld 3-instance RTL
+ * testbench, readme.pdf p.2-5).  grads/weights: [nranks][count]. */
+int ainic_allreduce_emulate(int nranks, float* grads, float* weights, void* weights_bf16, float* grads_out,
+                            size_t count, float lr, int codec, int bfp_mode, int algo, int ctas_per_rank,
+                            void* stream);
+
+/* ---------------------------------------------------------------- native data-parallel MLP trainer (C18)
+ * The training application of sw/mlp_mpi_example_f32.cpp:191-881 as a native executor: forward
+ * GEMMs, softmax loss, backward GEMMs on two streams and one fused all-reduce+SGD per layer on a
+ * third, per-layer events instead of the reference's two-deep request ring (:735-788).
+ * sizes = C[0..nlayers]; fuse: 0 none, 1 bias, 2 ReLU(mask), 3 bias+ReLU (:479-489). */
+typedef struct ainic_mlp ainic_mlp_t;
+int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlayers, const int* sizes, int mb, int fuse, float lr,
+                     float loss_weight, int codec, int bfp_mode, int algo);
+int ainic_mlp_destroy(ainic_mlp_t* m);
+/* what: 0 weight f32, 1 grad f32, 2 shadow bf16, 3 bias f32, 4 dbias f32, 5 act bf16, 6 dact bf16, 7 relu mask */
+void* ainic_mlp_buffer(ainic_mlp_t* m, int what, int layer);
+int ainic_mlp_sync_shadows(ainic_mlp_t* m, void* stream);
+int ainic_mlp_forward(ainic_mlp_t* m, const void* x_bf16, void* stream);
+int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t* labels, float* loss_out /*device, nullable*/,
+                   void* stream);
+int ainic_mlp_wait_updates(ainic_mlp_t* m, void* stream);
+unsigned long long ainic_mlp_launches(ainic_mlp_t* m);
+void* ainic_mlp_loss_ptr(ainic_mlp_t* m);
+
+/* ---------------------------------------------------------------- NIC-style command interface (C1a, C17)
+ * ainic_nic_* mirrors the driver of sw/mlp_mpi_example_f32.cpp:65-180: setup once, post up to 8
+ * requests that complete in order, each signalling one of 8 round-robin 64-byte done slots that
+ * the host polls.  backend: 0 = GPU (fused kernels over the communicator), 1 = host fake device
+ * (CPU threads + oracle math; lets the protocol be tested without a GPU). */
+typedef struct ainic_nic ainic_nic_t;
+typedef struct ainic_rqst { /* fpga_rqst, sw/mlp_mpi_example_f32.cpp:41-46 */
+  int idx;
+  int count;
+  float* buf;
+  volatile float* dev_buf;
+  uint64_t seq;
+} ainic_rqst_t;
+int ainic_nic_open(ainic_nic_t** out, ainic_comm_t* comm /*null for fake backend*/, int backend, int rank,
+                   int nranks);
+int ainic_nic_close(ainic_nic_t* nic);
+/* all_reduce_setup(done, count, node_id): programs total length + node id, returns the done buffer. */
+int ainic_nic_setup(ainic_nic_t* nic, size_t count, int codec, int bfp_mode, int algo, float lr);
+volatile uint32_t* ainic_nic_done_buffer(ainic_nic_t* nic); /* 8 slots x 16 words */
+/* all_reduce(buf, weight_out, flags, ...): flags != 0 = (re)load initial weights into the
+ * device-resident copy first (hw/weight_update.sv:624-637). */
+int ainic_nic_all_reduce(ainic_nic_t* nic, float* buf, float* weight_out, int flags, size_t count,
+                         ainic_rqst_t* rqst, void* stream);
+int ainic_nic_wait(ainic_nic_t* nic, ainic_rqst_t* rqst, double timeout_s /*<=0: forever*/);
+int ainic_nic_abort(ainic_nic_t* nic); /* kill_syn_e0, unconnected in the reference (hw/all_reduce.sv:83) */
+uint64_t ainic_nic_latency_ns(ainic_nic_t* nic);     /* get_all_reduce_latency */
+uint64_t ainic_nic_stall_ns(ainic_nic_t* nic);       /* get_host_stall_cycles */
+/* fake backend only: connect N fake NICs of one process into a ring. */
+int ainic_nic_fake_link(ainic_nic_t** nics, int n);
+
+/* MPI-style entry (sw/mlp_mpi_example_f32.cpp:615-620: MPI_Iallreduce(IN_PLACE, buf, count, FLOAT, SUM) + Wait) */
+int ainic_iallreduce(ainic_nic_t* nic, float* buf, size_t count, ainic_rqst_t* rqst, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AINIC_H_ */
