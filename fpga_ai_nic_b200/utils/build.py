@@ -58,13 +58,13 @@ CUDA_SOURCES = [
     "gemm/gemm_tcgen05.cu",
     "comm/comm.cu",
     "comm/nvls.cu",
-    "api/nic.cu",
+    "api/nic.cpp",
     "api/mlp.cu",
 ]
 ORACLE_SOURCES = [
     "oracle/oracle.cpp",
-    "oracle/fake_nic.cpp",
     "oracle/mini_mpi.cpp",
+    "api/nic.cpp",
 ]
 APPS = {"mlp_mpi_example_f32": ["apps/mlp_mpi_example_f32.cpp"]}
 
@@ -119,7 +119,8 @@ def build_cuda(force: bool = False, jobs: int | None = None) -> Path:
 
     def compile_one(so):
         s, o = so
-        _run([NVCC, *NVCC_FLAGS, "-c", str(s), "-o", str(o)], log=OBJDIR / (o.name + ".ptxas.log"))
+        extra = ["-x", "cu", "-DAINIC_WITH_CUDA"] if s.suffix == ".cpp" else []
+        _run([NVCC, *NVCC_FLAGS, *extra, "-c", str(s), "-o", str(o)], log=OBJDIR / (o.name + ".ptxas.log"))
 
     if todo:
         with cf.ThreadPoolExecutor(max_workers=jobs or min(8, os.cpu_count() or 4)) as ex:
