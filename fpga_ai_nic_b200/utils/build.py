@@ -60,6 +60,7 @@ CUDA_SOURCES = [
     "comm/nvls.cu",
     "api/nic.cpp",
     "api/mlp.cu",
+    "oracle/oracle.cpp",   # the fake NIC backend inside nic.cpp computes with the CPU oracle
 ]
 ORACLE_SOURCES = [
     "oracle/oracle.cpp",
