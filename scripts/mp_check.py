@@ -1,0 +1,179 @@
+"""Multi-process (one rank per GPU) correctness check, run under torchrun:
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+        --master-port 29511 scripts/mp_check.py
+
+1. fused all-reduce + SGD over IPC-mapped peer memory, every algorithm x codec, bit-exact against
+   the CPU oracle (gradients of all ranks are gathered with NCCL only to build the expectation);
+2. the NIC command interface on the GPU backend (10 requests, 8 done slots, in order);
+3. the native DP trainer: replicas bit-identical after several steps, loss falls, and the weights
+   match a CPU oracle run of the same data-parallel SGD within bf16 GEMM tolerance.
+Prints one JSON line per check on rank 0 and exits non-zero on failure.
+"""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer  # noqa: E402
+from fpga_ai_nic_b200.ops import kernels as K  # noqa: E402
+from fpga_ai_nic_b200.ops import oracle as O  # noqa: E402
+from fpga_ai_nic_b200.parallel.comm import Communicator  # noqa: E402
+from fpga_ai_nic_b200.parallel.nic import Nic  # noqa: E402
+
+rank = int(os.environ.get("RANK", 0))
+world = int(os.environ.get("WORLD_SIZE", 1))
+local = int(os.environ.get("LOCAL_RANK", 0))
+torch.cuda.set_device(local)
+if world > 1:
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+fails = []
+
+
+def say(**kw):
+    if rank == 0:
+        print(json.dumps(kw), flush=True)
+
+
+def gather(t: torch.Tensor) -> torch.Tensor:
+    if world == 1:
+        return t[None].cpu()
+    out = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(out, t)
+    return torch.stack(out).cpu()
+
+
+def all_ok(ok: bool) -> bool:
+    if world == 1:
+        return ok
+    t = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(t.item())
+
+
+comm = Communicator(512 << 20)
+
+# ------------------------------------------------------------------ 1. fused all-reduce + SGD
+CASES = [("oneshot", "f32", 0), ("oneshot", "bfp", O.CLEAN), ("oneshot", "bfp", O.HW_EXACT), ("oneshot", "mxfp8", 0),
+         ("oneshot", "bf16", 0), ("twoshot", "f32", 0), ("twoshot", "bfp", O.CLEAN), ("twoshot", "bfp", O.HW_EXACT),
+         ("twoshot", "mxfp8", 0), ("twoshot", "bf16", 0), ("ring", "f32", 0), ("ring", "bfp", O.HW_EXACT)]
+count_max = 1 << 20
+g_heap = comm.empty(count_max)
+w_heap = comm.empty(count_max)
+sh = torch.empty(count_max, dtype=torch.bfloat16, device="cuda")
+for count in (8192 * 5 + 777, 1 << 20):
+    for it, (algo, codec, mode) in enumerate(CASES):
+        gen = torch.Generator().manual_seed(100 * it + rank)
+        g = torch.randn(count, generator=gen) * 1e-3
+        w0 = torch.randn(count, generator=torch.Generator().manual_seed(7))
+        gv, wv = g_heap[:count], w_heap[:count]
+        gv.copy_(g)
+        wv.copy_(w0)
+        all_g = gather(gv)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        comm.allreduce_fused(gv, wv, 0.1, sh[:count], codec=K.CODEC_NAMES[codec], bfp_mode=mode, algo=K.ALGO_NAMES[algo])
+        torch.cuda.synchronize()
+        want = O.allreduce(all_g, "exact" if (codec == "f32" and algo != "ring") else algo, K.CODEC_NAMES[codec], mode)
+        w_want = O.sgd(w0, want[rank], 0.1)
+        ok = torch.equal(wv.cpu(), w_want) and torch.equal(sh[:count].cpu(), w_want.to(torch.bfloat16))
+        ok = all_ok(ok)
+        ctr = comm.counters()
+        say(check="allreduce_fused", algo=algo, codec=codec, mode=mode, count=count, world=world, ok=ok,
+            timeouts=ctr["timeouts"], last_us=ctr["last_ns"] / 1e3)
+        if not ok or ctr["timeouts"]:
+            fails.append(("allreduce", algo, codec, mode, count))
+        if world > 1:
+            dist.barrier()
+
+# ------------------------------------------------------------------ 2. NIC command interface, GPU backend
+nic = Nic("gpu", comm=comm, rank=rank, nranks=world)
+count = 1 << 16
+nic.setup(count, codec="bfp", bfp_mode=O.CLEAN, algo="twoshot", lr=0.5)
+bufs = [comm.empty(count) for _ in range(10)]
+wts = [comm.empty(count) for _ in range(10)]
+for i in range(10):
+    bufs[i].fill_(float(i + 1) * (rank + 1))
+    wts[i].zero_()
+torch.cuda.synchronize()
+if world > 1:
+    dist.barrier()
+rqs = []
+ok = True
+for i in range(10):
+    if i >= 8:
+        nic.wait(rqs[i - 8], 30)          # at most 8 outstanding
+    rqs.append(nic.all_reduce(bufs[i], wts[i], flags=int(i == 0)))
+    ok &= rqs[-1].idx == i % 8
+for i in range(10):
+    nic.wait(rqs[i], 30)
+torch.cuda.synchronize()
+tot = sum(r + 1 for r in range(world))
+for i in range(10):
+    ok &= bool(torch.allclose(wts[i], torch.full_like(wts[i], -0.5 * (i + 1) * tot), rtol=2e-2))
+rq = nic.iallreduce(bufs[0])
+nic.wait(rq, 30)
+torch.cuda.synchronize()
+ok &= bool(torch.allclose(bufs[0], torch.full_like(bufs[0], 1.0 * tot), rtol=2e-2))
+ok = all_ok(ok)
+say(check="nic_gpu", ok=ok, latency_us=nic.latency_ns() / 1e3, stall_us=nic.stall_ns() / 1e3)
+if not ok:
+    fails.append(("nic",))
+nic.close()
+
+# ------------------------------------------------------------------ 3. native DP trainer
+for codec in ("f32", "bfp"):
+    cfg = MLPConfig(sizes=[256, 512, 384, 128], mb=256, fuse=0, lr=0.5, loss_weight=1.0, codec=codec)
+    tr = MLPTrainer(cfg, comm=comm)
+    gen = torch.Generator().manual_seed(4321 + rank)
+    x = torch.rand(cfg.mb, cfg.sizes[0], generator=gen) * 2 - 1
+    y = torch.randint(0, cfg.sizes[-1], (cfg.mb,), generator=gen, dtype=torch.int32)
+    xb, yd = K.cast_bf16(x.cuda()), y.cuda()
+    w_init = [tr.buffer("weight", l).cpu().clone() for l in range(cfg.nlayers)]
+    losses = []
+    steps = 4
+    for _ in range(steps):
+        tr.step(xb, yd)
+        tr.wait()
+        torch.cuda.synchronize()
+        losses.append(float(tr.loss_dev.item()) / cfg.mb)
+    ident = True
+    for l in range(cfg.nlayers):
+        allw = gather(tr.buffer("weight", l).reshape(-1))
+        ident &= all(torch.equal(allw[r], allw[0]) for r in range(world))
+    # CPU oracle of the same data-parallel SGD (fp32 everywhere)
+    xs, ys = gather(x.cuda()), gather(y.cuda())
+    W = [w.clone() for w in w_init]
+    for _ in range(steps):
+        grads = [torch.zeros_like(w) for w in W]
+        for r in range(world):
+            acts = [xs[r].bfloat16().float()]
+            for l in range(cfg.nlayers):
+                acts.append(O.fc_fwd(acts[-1], W[l].bfloat16().float())[0].bfloat16().float())
+            _, _, d = O.softmax_loss(acts[-1], ys[r], cfg.loss_weight)
+            d = d.bfloat16().float()
+            for l in reversed(range(cfg.nlayers)):
+                dx, dw, _ = O.fc_bwd(acts[l], W[l].bfloat16().float(), d, need_dx=l > 0)
+                grads[l] += dw
+                if l > 0:
+                    d = dx.bfloat16().float()
+        W = [O.sgd(W[l], grads[l], cfg.lr) for l in range(cfg.nlayers)]
+    rel = max(((tr.buffer("weight", l).cpu() - W[l]).norm() / (W[l] - w_init[l]).norm().clamp_min(1e-12)).item()
+              for l in range(cfg.nlayers))
+    ok = ident and losses[-1] < losses[0] and rel < (0.02 if codec == "f32" else 0.08)
+    ok = all_ok(ok)
+    say(check="mlp_trainer", codec=codec, world=world, ok=ok, identical_replicas=ident, losses=losses,
+        update_rel_err_vs_oracle=rel, timeouts=comm.counters()["timeouts"])
+    if not ok:
+        fails.append(("mlp", codec))
+    tr.close()
+
+if world > 1:
+    dist.barrier()
+    dist.destroy_process_group()
+say(check="summary", world=world, failures=fails)
+sys.exit(1 if fails else 0)
