@@ -139,6 +139,8 @@ def cuda() -> C.CDLL:
     lib.ainic_comm_counters.argtypes = [vp, c_u64p]
     lib.ainic_allreduce_fused.argtypes = [vp, C.POINTER(AllreduceArgs), vp]
     lib.ainic_allreduce_emulate.argtypes = [C.c_int, vp, vp, vp, vp, sz, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+    lib.ainic_allreduce_emulate_noalloc.argtypes = [C.c_int, vp, vp, vp, vp, sz, C.c_float, C.c_int, C.c_int, C.c_int,
+                                                    C.c_int, vp, C.c_char_p, sz]
     lib.ainic_mlp_create.argtypes = [C.POINTER(vp), vp, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_float,
                                      C.c_float, C.c_int, C.c_int, C.c_int]
     lib.ainic_mlp_destroy.argtypes = [vp]

@@ -58,6 +58,7 @@ CUDA_SOURCES = [
     "gemm/gemm_tcgen05.cu",
     "comm/comm.cu",
     "comm/nvls.cu",
+    "comm/emulate_noalloc.cu",
     "api/nic.cpp",
     "api/mlp.cu",
     "oracle/oracle.cpp",   # the fake NIC backend inside nic.cpp computes with the CPU oracle

@@ -125,6 +125,21 @@ int ainic_allreduce_emulate(int nranks, float* grads, float* weights, void* weig
                             size_t count, float lr, int codec, int bfp_mode, int algo, int ctas_per_rank,
                             void* stream);
 
+/* Same emulation for callers that may not allocate device memory (a thread running beside a stream
+ * capture, a service whose HBM is fully claimed by its own pool, a loop that cannot take cudaFree's
+ * device-wide sync).  No counterpart in the reference: the FPGA owns its buffers statically.
+ * All scratch (staging, flags, counters) lives in one 2 MiB static __device__ array per GPU and
+ * the rank contexts travel by value, so the call never allocates.  Limits: nranks <=
+ * AINIC_NOALLOC_MAX_RANKS, count <= AINIC_NOALLOC_MAX_COUNT values per rank; larger requests
+ * return AINIC_ERR_ARG with the reason in errbuf (nullable).  The first call on a device resolves
+ * the scratch address and must precede any stream capture; calls share the scratch, so calls whose
+ * GPU work overlaps race - serialise them.  Returns after the kernel has finished. */
+#define AINIC_NOALLOC_MAX_RANKS 4
+#define AINIC_NOALLOC_MAX_COUNT 32768
+int ainic_allreduce_emulate_noalloc(int nranks, float* grads, float* weights, void* weights_bf16, float* grads_out,
+                                    size_t count, float lr, int codec, int bfp_mode, int algo, int ctas_per_rank,
+                                    void* stream, char* errbuf, size_t errbuf_len);
+
 /* ---------------------------------------------------------------- native data-parallel MLP trainer (C18)
  * The training application of sw/mlp_mpi_example_f32.cpp:191-881 as a native executor: forward
  * GEMMs, softmax loss, backward GEMMs on two streams and one fused all-reduce+SGD per layer on a
