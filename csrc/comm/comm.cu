@@ -187,9 +187,18 @@ static int default_ctas(int algo, int nranks, size_t count) {
   const size_t frames = bfp_frames(count);
   size_t work = frames;  // frames per rank per phase
   if (algo == AINIC_ALGO_RING) work = (frames + (size_t)nranks * kSliceFrames - 1) / ((size_t)nranks * kSliceFrames);
-  else work = (frames + 15) / 16;  // 16 warps per CTA, one frame each
+  else work = (frames + 31) / 32;  // 16 warps per CTA, at least two frames per warp
   size_t ctas = work < 1 ? 1 : work;
-  const size_t cap = 64;
+  // The kernels are memory/latency bound: a 16 MiB bucket on 64 CTAs took ~70 us, the same bytes on
+  // every SM ~15 us.  Run wide and short; the trainer can narrow it with AINIC_COMM_CTAS.
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+  }
+  const size_t cap = (size_t)sms;
   if (ctas > cap) ctas = cap;
   return (int)ctas;
 }

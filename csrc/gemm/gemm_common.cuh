@@ -1,0 +1,201 @@
+// Pieces shared by the 1-CTA and 2-CTA (cta_group::2) tcgen05 GEMM kernels: tile constants,
+// shared-memory / instruction descriptors, the fused epilogue, TMA tensor-map construction.
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdlib.h>
+
+#include "../../include/ainic.h"
+#include "../common/ptx.cuh"
+
+namespace ainic {
+namespace gemm {
+
+using namespace ptx;
+
+constexpr int BLOCK_M = 128;   // rows per CTA (TMEM has 128 lanes)
+constexpr int BLOCK_K = 64;    // 64 bf16 = 128 B = one swizzle span
+constexpr int UMMA_K = 16;
+constexpr int kThreads = 192;  // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2-5 epilogue
+constexpr int kSmemBudget = 220 * 1024;
+
+struct EpiParams {
+  void* c;                 // output, row-major [M][ldc]; bf16 or fp32
+  const float* bias;       // [N] or null (added before activation)
+  uint8_t* mask_out;       // [M][ldc] or null: 1 where the (biased) result is > 0 (ReLU mask)
+  const uint8_t* mask_in;  // [M][ldc] or null: output zeroed where mask_in == 0 (ReLU backward)
+  float alpha;             // result scale (fp32 output only)
+  int relu;                // apply max(0, x)
+  int accumulate;          // fp32 output only: c += result
+  int M, N, K, ldc;
+};
+
+// Shared-memory matrix descriptor (sm_100 format, version 1, SWIZZLE_128B).
+//   K-major operand : rows of 128 B, 8-row core-matrix groups SBO = 1024 B apart (LBO unused).
+//   MN-major operand: 64-element (128 B) spans along MN, one span per k row; k groups of 8 rows are
+//                     SBO = 1024 B apart, the next 64 MN elements start LBO = 8192 B further.
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  return d;
+}
+template <bool MN_MAJOR>
+__device__ __forceinline__ uint64_t operand_desc(uint32_t tile_addr, int k) {
+  // advance by one UMMA_K = 16 elements: 32 B inside the swizzle span (K-major) or 16 k-rows (MN-major)
+  return MN_MAJOR ? make_desc(tile_addr + k * (UMMA_K * 128), 8192, 1024) : make_desc(tile_addr + k * (UMMA_K * 2), 16, 1024);
+}
+
+// kind::f16 instruction descriptor: bf16 x bf16 -> fp32, M x N, operand majors.
+template <int M, int N, bool A_MN, bool B_MN>
+__host__ __device__ constexpr uint32_t make_idesc() {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// Drain one 128 x BLOCK_N accumulator: thread `lane` of the warp owning TMEM lane quarter q reads
+// row (32 q + lane) 32 columns at a time and writes it with the fused epilogue.
+template <int BLOCK_N, bool OUT_F32>
+__device__ __forceinline__ void epilogue_store(const EpiParams& ep, uint32_t taddr, int row, int n0) {
+  const bool row_ok = row < ep.M;
+#pragma unroll 1
+  for (int c = 0; c < BLOCK_N / 32 + (BLOCK_N % 32 ? 1 : 0); ++c) {
+    uint32_t r[32];
+    if (BLOCK_N % 32 == 0 || c < BLOCK_N / 32) {
+      tmem_ld_32x32b_x32(taddr + c * 32, r);
+    } else {
+      // 16-column tail (BLOCK_N % 32 == 16): read the last 32 columns, keep the upper half.
+      tmem_ld_32x32b_x32(taddr + c * 32 - 16, r);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) r[j] = r[j + 16];
+    }
+    tmem_ld_wait();
+    const int ncols = (BLOCK_N % 32 == 0 || c < BLOCK_N / 32) ? 32 : 16;
+    const int col0 = n0 + c * 32;
+    if (row_ok && col0 < ep.N) {
+      const size_t off = (size_t)row * ep.ldc + col0;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {  // groups of 8 columns
+        if (g * 8 < ncols && col0 + g * 8 < ep.N) {
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+          if constexpr (OUT_F32) {
+            float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.c) + off + g * 8);
+            if (ep.alpha != 1.0f) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] *= ep.alpha;
+            }
+            if (ep.accumulate) {
+              float4 o0 = dst[0], o1 = dst[1];
+              v[0] += o0.x; v[1] += o0.y; v[2] += o0.z; v[3] += o0.w;
+              v[4] += o1.x; v[5] += o1.y; v[6] += o1.z; v[7] += o1.w;
+            }
+            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+            dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+          } else {
+            if (ep.bias) {
+              const float4 b0 = *reinterpret_cast<const float4*>(ep.bias + col0 + g * 8);
+              const float4 b1 = *reinterpret_cast<const float4*>(ep.bias + col0 + g * 8 + 4);
+              v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+              v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+            }
+            if (ep.mask_out) {
+              uint32_t lo = 0, hi = 0;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                lo |= (v[j] > 0.0f ? 1u : 0u) << (8 * j);
+                hi |= (v[4 + j] > 0.0f ? 1u : 0u) << (8 * j);
+              }
+              *reinterpret_cast<uint2*>(ep.mask_out + off + g * 8) = make_uint2(lo, hi);
+            }
+            if (ep.relu) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.0f);
+            }
+            if (ep.mask_in) {
+              const uint2 mk = *reinterpret_cast<const uint2*>(ep.mask_in + off + g * 8);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                if (((mk.x >> (8 * j)) & 0xFFu) == 0u) v[j] = 0.0f;
+                if (((mk.y >> (8 * j)) & 0xFFu) == 0u) v[4 + j] = 0.0f;
+              }
+            }
+            uint4 o;
+            o.x = pack_bf16(v[0], v[1]);
+            o.y = pack_bf16(v[2], v[3]);
+            o.z = pack_bf16(v[4], v[5]);
+            o.w = pack_bf16(v[6], v[7]);
+            *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(ep.c) + off + g * 8) = o;
+          }
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// bf16 row-major [rows][cols] (cols contiguous, leading dimension ld elements); box = box_c x box_r.
+inline int make_tmap(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_c,
+                     uint32_t box_r) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return AINIC_ERR_CUDA;
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {ld * 2};
+  cuuint32_t box[2] = {box_c, box_r};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? AINIC_OK : AINIC_ERR_CUDA;
+}
+
+inline int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return n;
+}
+
+inline bool pdl_enabled() {
+  static const bool on = !(getenv("AINIC_GEMM_PDL") && atoi(getenv("AINIC_GEMM_PDL")) == 0);
+  return on;
+}
+
+// Launch entry of the 2-CTA kernels (gemm_tcgen05_2cta.cu); returns AINIC_ERR_UNSUPPORTED for
+// combinations that have no 2-CTA instantiation.
+int launch_2cta(int layout, const void* a, int lda, const void* b, int ldb, const EpiParams& ep, int block_n,
+                int max_ctas, cudaStream_t stream);
+
+}  // namespace gemm
+}  // namespace ainic

@@ -7,41 +7,20 @@
 // straight into the flat gradient bucket the all-reduce engine consumes (the buffer the reference
 // hands to the NIC, sw/mlp_mpi_example_f32.cpp:754), optionally accumulating or pre-scaling.
 //
-// Structure: persistent, warp-specialised, one CTA per SM.
+// This file: the 1-CTA kernel (tcgen05.mma.cta_group::1, 128 x BLOCK_N tiles) and the public entry
+// point, which prefers the 2-CTA kernel (gemm_tcgen05_2cta.cu, 256 x BLOCK_N tiles over an SM pair)
+// when the shape allows it.  Structure of both: persistent, warp-specialised, one CTA per SM.
 //   warp 0   : TMA producer (one elected lane)         global -> 128B-swizzled smem ring
-//   warp 1   : TMEM allocator + MMA issuer (one lane)  tcgen05.mma.cta_group::1.kind::f16, 128xBLOCK_Nx16
+//   warp 1   : TMEM allocator + MMA issuer (one lane)  tcgen05.mma kind::f16
 //   warps 2-5: epilogue                                tcgen05.ld 32x32b -> registers -> global
-// Two TMEM accumulator stages let the epilogue of tile i overlap the main loop of tile i+1.
-#include <cuda.h>
-#include <cuda_bf16.h>
-#include <cuda_runtime.h>
-#include <stdint.h>
+// Two TMEM accumulator stages let the epilogue of tile i overlap the main loop of tile i+1; the
+// prologue overlaps the previous kernel's tail through programmatic dependent launch.
 #include <stdio.h>
 
-#include "../common/ptx.cuh"
-#include "../../include/ainic.h"
+#include "gemm_common.cuh"
 
 namespace ainic {
 namespace gemm {
-
-using namespace ptx;
-
-constexpr int BLOCK_M = 128;
-constexpr int BLOCK_K = 64;  // 64 bf16 = 128 B = one swizzle span
-constexpr int UMMA_K = 16;
-constexpr int kThreads = 192;
-constexpr int kSmemBudget = 220 * 1024;
-
-struct EpiParams {
-  void* c;              // output, row-major [M][ldc]; bf16 or fp32
-  const float* bias;    // [N] or null (added before activation)
-  uint8_t* mask_out;    // [M][ldc] or null: 1 where the (biased) result is > 0 (ReLU mask)
-  const uint8_t* mask_in;  // [M][ldc] or null: output zeroed where mask_in == 0 (ReLU backward)
-  float alpha;          // result scale (fp32 output only)
-  int relu;             // apply max(0, x)
-  int accumulate;       // fp32 output only: c += result
-  int M, N, K, ldc;
-};
 
 __host__ __device__ constexpr int stage_bytes(int block_n) { return BLOCK_M * BLOCK_K * 2 + block_n * BLOCK_K * 2; }
 __host__ __device__ constexpr int num_stages(int block_n) {
@@ -49,33 +28,6 @@ __host__ __device__ constexpr int num_stages(int block_n) {
 }
 __host__ __device__ constexpr uint32_t tmem_cols(int block_n) {
   return 2 * block_n <= 32 ? 32u : 2 * block_n <= 64 ? 64u : 2 * block_n <= 128 ? 128u : 2 * block_n <= 256 ? 256u : 512u;
-}
-
-// Shared-memory matrix descriptor (sm_100 format, version 1, SWIZZLE_128B).
-__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
-  d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
-  return d;
-}
-
-template <int BLOCK_N, bool A_MN, bool B_MN>
-__host__ __device__ constexpr uint32_t make_idesc() {
-  return (1u << 4)                          // D format: F32
-         | (1u << 7)                        // A format: BF16
-         | (1u << 10)                       // B format: BF16
-         | ((A_MN ? 1u : 0u) << 15)         // A major
-         | ((B_MN ? 1u : 0u) << 16)         // B major
-         | ((uint32_t)(BLOCK_N >> 3) << 17)  // N
-         | ((uint32_t)(BLOCK_M >> 4) << 24); // M
-}
-
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&v);
 }
 
 template <int BLOCK_N, bool A_MN, bool B_MN, bool OUT_F32>
@@ -125,6 +77,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  // Programmatic dependent launch: everything above (barrier init, TMEM allocation, tensor-map
+  // prefetch) overlaps the tail of the previous kernel in the stream; from here on we touch memory
+  // it may have written.
+  griddep_wait();
+  griddep_launch_dependents();
 
   if (warp == 0) {
     // ===================================================== TMA producer
@@ -159,7 +116,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   } else if (warp == 1) {
     // ===================================================== MMA issuer
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc<BLOCK_N, A_MN, B_MN>();
+      constexpr uint32_t idesc = make_idesc<BLOCK_M, BLOCK_N, A_MN, B_MN>();
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -174,15 +131,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           const uint32_t a_addr = smem_u32(smem_a + stage * kABytes);
           const uint32_t b_addr = smem_u32(smem_b + stage * kBBytes);
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            // K-major: 16 elements = 32 B inside the 128 B swizzle span.
-            // MN-major: 16 k-rows of 128 B = two 1024 B core-matrix groups.
-            const uint64_t da = A_MN ? make_desc(a_addr + k * (UMMA_K * 128), 8192, 1024)
-                                     : make_desc(a_addr + k * (UMMA_K * 2), 16, 1024);
-            const uint64_t db = B_MN ? make_desc(b_addr + k * (UMMA_K * 128), 8192, 1024)
-                                     : make_desc(b_addr + k * (UMMA_K * 2), 16, 1024);
-            umma_f16(tmem_d, da, db, idesc, (uint32_t)((kb | k) != 0));
-          }
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+            umma_f16(tmem_d, operand_desc<A_MN>(a_addr, k), operand_desc<B_MN>(b_addr, k), idesc, (uint32_t)((kb | k) != 0));
           umma_commit(&empty_bar[stage]);
           if (kb == k_blocks - 1) umma_commit(&tmem_full[acc]);
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -200,83 +150,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const int n0 = (tile / m_tiles) * BLOCK_N;
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      const int row = m0 + quarter * 32 + lane;
-      const bool row_ok = row < ep.M;
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N);
-#pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32 + (BLOCK_N % 32 ? 1 : 0); ++c) {
-        uint32_t r[32];
-        if (BLOCK_N % 32 == 0 || c < BLOCK_N / 32) {
-          tmem_ld_32x32b_x32(taddr + c * 32, r);
-        } else {
-          // 16-column tail (BLOCK_N % 32 == 16): read 32 columns, the upper half is ignored below.
-          tmem_ld_32x32b_x32(taddr + c * 32 - 16, r);
-#pragma unroll
-          for (int j = 0; j < 16; ++j) r[j] = r[j + 16];
-        }
-        tmem_ld_wait();
-        const int ncols = (BLOCK_N % 32 == 0 || c < BLOCK_N / 32) ? 32 : 16;
-        const int col0 = n0 + c * 32;
-        if (row_ok && col0 < ep.N) {
-          const size_t off = (size_t)row * ep.ldc + col0;
-#pragma unroll
-          for (int g = 0; g < 4; ++g) {  // groups of 8 columns
-            if (g * 8 < ncols && col0 + g * 8 < ep.N) {
-              float v[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
-              if constexpr (OUT_F32) {
-                float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.c) + off + g * 8);
-                if (ep.alpha != 1.0f) {
-#pragma unroll
-                  for (int j = 0; j < 8; ++j) v[j] *= ep.alpha;
-                }
-                if (ep.accumulate) {
-                  float4 o0 = dst[0], o1 = dst[1];
-                  v[0] += o0.x; v[1] += o0.y; v[2] += o0.z; v[3] += o0.w;
-                  v[4] += o1.x; v[5] += o1.y; v[6] += o1.z; v[7] += o1.w;
-                }
-                dst[0] = make_float4(v[0], v[1], v[2], v[3]);
-                dst[1] = make_float4(v[4], v[5], v[6], v[7]);
-              } else {
-                if (ep.bias) {
-                  const float4 b0 = *reinterpret_cast<const float4*>(ep.bias + col0 + g * 8);
-                  const float4 b1 = *reinterpret_cast<const float4*>(ep.bias + col0 + g * 8 + 4);
-                  v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-                  v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
-                }
-                if (ep.mask_out) {
-                  uint32_t lo = 0, hi = 0;
-#pragma unroll
-                  for (int j = 0; j < 4; ++j) {
-                    lo |= (v[j] > 0.0f ? 1u : 0u) << (8 * j);
-                    hi |= (v[4 + j] > 0.0f ? 1u : 0u) << (8 * j);
-                  }
-                  *reinterpret_cast<uint2*>(ep.mask_out + off + g * 8) = make_uint2(lo, hi);
-                }
-                if (ep.relu) {
-#pragma unroll
-                  for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.0f);
-                }
-                if (ep.mask_in) {
-                  const uint2 mk = *reinterpret_cast<const uint2*>(ep.mask_in + off + g * 8);
-#pragma unroll
-                  for (int j = 0; j < 4; ++j) {
-                    if (((mk.x >> (8 * j)) & 0xFFu) == 0u) v[j] = 0.0f;
-                    if (((mk.y >> (8 * j)) & 0xFFu) == 0u) v[4 + j] = 0.0f;
-                  }
-                }
-                uint4 o;
-                o.x = pack_bf16(v[0], v[1]);
-                o.y = pack_bf16(v[2], v[3]);
-                o.z = pack_bf16(v[4], v[5]);
-                o.w = pack_bf16(v[6], v[7]);
-                *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(ep.c) + off + g * 8) = o;
-              }
-            }
-          }
-        }
-      }
+      epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
@@ -287,50 +162,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (warp == 1) tmem_dealloc<kTmemCols>(tmem_base);
-}
-
-// ------------------------------------------------------------------------------------------ host
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
-        qres != cudaDriverEntryPointSuccess)
-      return nullptr;
-    fn = reinterpret_cast<EncodeTiledFn>(p);
+  if (warp == 1) {
+    __syncwarp();
+    tmem_dealloc<kTmemCols>(tmem_base);
   }
-  return fn;
-}
-
-// bf16 row-major [rows][cols] (cols contiguous, leading dimension ld elements); box = box_c x box_r.
-static int make_tmap(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_c,
-                     uint32_t box_r) {
-  EncodeTiledFn fn = get_encode_fn();
-  if (!fn) return AINIC_ERR_CUDA;
-  cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstride[1] = {ld * 2};
-  cuuint32_t box[2] = {box_c, box_r};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? AINIC_OK : AINIC_ERR_CUDA;
-}
-
-static int g_num_sms = 0;
-static int num_sms() {
-  if (!g_num_sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-  }
-  return g_num_sms;
 }
 
 template <int BLOCK_N, bool A_MN, bool B_MN, bool OUT_F32>
@@ -356,16 +191,27 @@ static int launch(const void* a, int lda, const void* b, int ldb, const EpiParam
   int grid = num_sms();
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (tiles < grid) grid = tiles;
-  kern<<<grid, kThreads, smem, stream>>>(ta, tb, ep);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  if (cudaLaunchKernelEx(&cfg, kern, ta, tb, ep) != cudaSuccess) return AINIC_ERR_CUDA;
   return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
 }
 
-// Wave efficiency of a BLOCK_N choice: useful work / (waves * grid * tile work).
-static double wave_eff(int M, int N, int bn, int sms) {
-  const long tiles = (long)((M + BLOCK_M - 1) / BLOCK_M) * ((N + bn - 1) / bn);
-  const long waves = (tiles + sms - 1) / sms;
+// Wave efficiency of a tile choice: useful work / (waves * slots * tile work).  `rows` is the tile
+// height (128 for 1-CTA, 256 for a CTA pair), `slots` the number of tiles that run concurrently.
+static double wave_eff(int M, int N, int rows, int bn, int slots) {
+  const long tiles = (long)((M + rows - 1) / rows) * ((N + bn - 1) / bn);
+  const long waves = (tiles + slots - 1) / slots;
   // fixed per-tile cost (prologue/epilogue) favours fewer, larger tiles a little
-  return ((double)M * N) / ((double)waves * sms * BLOCK_M * (bn + 24.0));
+  return ((double)M * N) / ((double)waves * slots * rows * (bn + 24.0));
 }
 
 }  // namespace gemm
@@ -377,6 +223,7 @@ using namespace ainic::gemm;
   case BN:                                                                                 \
     return launch<BN, AMN, BMN, F32>(a, lda, b, ldb, ep, max_ctas, (cudaStream_t)stream);
 
+// block_n: 0 = choose; > 0 = 1-CTA kernel with that tile width; < 0 = 2-CTA kernel with width -block_n.
 extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b, int ldb, void* c, int ldc, int M,
                                int N, int K, const ainic_gemm_epilogue_t* epi, int block_n, int max_ctas,
                                void* stream) {
@@ -395,16 +242,28 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
     ep.alpha = epi->alpha;
   }
   const int sms = (max_ctas > 0 && max_ctas < num_sms()) ? max_ctas : num_sms();
-  if (block_n <= 0) {
-    const int cand_kk[] = {256, 208, 128};
-    const int cand_mn[] = {256, 192, 128};
-    const int* cand = (layout == AINIC_GEMM_NT) ? cand_kk : cand_mn;
+  if (block_n == 0) {
+    // The 2-CTA kernels are correct but currently slower than the 1-CTA ones on the reference shape
+    // (profiles/gemm_2cta_ncu.md), so the heuristic only considers them on request.
+    static const bool allow_2cta = getenv("AINIC_GEMM_2CTA") && atoi(getenv("AINIC_GEMM_2CTA")) == 1;
+    const int cand1_kk[] = {256, 208, 128}, cand1_mn[] = {256, 192, 128};
+    const int cand2_kk[] = {256, 208}, cand2_mn[] = {256, 128};
+    const bool kk = layout == AINIC_GEMM_NT;
     double best = -1.0;
     for (int i = 0; i < 3; ++i) {
-      double e = wave_eff(M, N, cand[i], sms);
-      if (e > best * 1.02) { best = e; block_n = cand[i]; }
+      const int bn = kk ? cand1_kk[i] : cand1_mn[i];
+      const double e = wave_eff(M, N, 128, bn, sms) * 0.80;   // 1-CTA main loop is smem-bandwidth bound
+      if (e > best * 1.02) { best = e; block_n = bn; }
+    }
+    if (allow_2cta && M >= 256 && sms >= 2) {
+      for (int i = 0; i < 2; ++i) {
+        const int bn = kk ? cand2_kk[i] : cand2_mn[i];
+        const double e = wave_eff(M, N, 256, bn, sms / 2);
+        if (e > best * 1.02) { best = e; block_n = -bn; }
+      }
     }
   }
+  if (block_n < 0) return launch_2cta(layout, a, lda, b, ldb, ep, -block_n, max_ctas, (cudaStream_t)stream);
   switch (layout) {
     case AINIC_GEMM_NT:  // C = A[M,K] . B[N,K]^T, bf16 out
       switch (block_n) {

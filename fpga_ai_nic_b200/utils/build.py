@@ -56,6 +56,7 @@ CUDA_SOURCES = [
     "optim/sgd.cu",
     "nn/softmax.cu",
     "gemm/gemm_tcgen05.cu",
+    "gemm/gemm_tcgen05_2cta.cu",
     "comm/comm.cu",
     "comm/nvls.cu",
     "comm/emulate_noalloc.cu",

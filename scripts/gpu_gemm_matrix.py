@@ -15,8 +15,10 @@ import time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-VARIANTS = [("fwd", bn) for bn in (256, 208, 128)] + [("bwd_data", bn) for bn in (256, 192, 128)] + \
-           [("bwd_weight", bn) for bn in (256, 192, 128)]
+# block_n > 0: 1-CTA kernel; < 0: 2-CTA (cta_group::2) kernel with tile width -block_n; 0: heuristic
+VARIANTS = [("fwd", bn) for bn in (0, -256, -208, -128, 256, 208, 128)] + \
+           [("bwd_data", bn) for bn in (0, -256, -128, 256, 192, 128)] + \
+           [("bwd_weight", bn) for bn in (0, -256, -128, 256, 192, 128)]
 SHAPES = [(128, 256, 64), (256, 512, 256), (384, 1024, 1088), (1792, 2048, 2048)]
 
 
@@ -110,7 +112,7 @@ def main() -> None:
         status = "OK" if last["rc"] == 0 and last["results"] and all(r["ok"] for r in last["results"]) else "FAIL"
         perf = next((f'{r["tflops"]:.0f} TFLOPS ({r["ms"]:.3f} ms, cuBLAS {r.get("cublas_ms", 0):.3f} ms)'
                      for r in last["results"] if "tflops" in r), "")
-        print(f"{kind:11s} bn={bn:3d} {status} {perf} [{time.time() - t0:.0f}s]", flush=True)
+        print(f"{kind:11s} bn={bn:4d} {status} {perf} [{time.time() - t0:.0f}s]", flush=True)
         if status == "FAIL":
             print(json.dumps(last)[:3000], flush=True)
     with open(os.path.join(ROOT, "gpurun_out", "gemm_matrix.json"), "w") as f:

@@ -61,7 +61,7 @@ GEMM_SHAPES = [(128, 256, 64), (256, 512, 256), (384, 1024, 1088), (1792, 2048, 
 
 
 @pytest.mark.parametrize("mb,n,k", GEMM_SHAPES)
-@pytest.mark.parametrize("block_n", [0, 128, 208, 256])
+@pytest.mark.parametrize("block_n", [0, 128, 208, 256, -128, -208, -256])   # < 0: 2-CTA kernel
 def test_gemm_fwd(K, mb, n, k, block_n):
     torch.manual_seed(0)
     x = (torch.randn(mb, k, device="cuda") * 0.5).bfloat16()
@@ -74,7 +74,7 @@ def test_gemm_fwd(K, mb, n, k, block_n):
 
 
 @pytest.mark.parametrize("mb,n,k", GEMM_SHAPES)
-@pytest.mark.parametrize("block_n", [0, 128, 192, 256])
+@pytest.mark.parametrize("block_n", [0, 128, 192, 256, -128, -256])
 def test_gemm_bwd_data(K, mb, n, k, block_n):
     torch.manual_seed(1)
     dy = (torch.randn(mb, n, device="cuda") * 0.5).bfloat16()
@@ -87,7 +87,7 @@ def test_gemm_bwd_data(K, mb, n, k, block_n):
 
 
 @pytest.mark.parametrize("mb,n,k", GEMM_SHAPES)
-@pytest.mark.parametrize("block_n", [0, 128, 192, 256])
+@pytest.mark.parametrize("block_n", [0, 128, 192, 256, -128, -256])
 def test_gemm_bwd_weight(K, mb, n, k, block_n):
     torch.manual_seed(2)
     dy = (torch.randn(mb, n, device="cuda") * 0.05).bfloat16()
