@@ -84,6 +84,13 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    g_nvls = None
+    if world > 1 and comm.enable_nvls(max_count * 4 + (4 << 20)):
+        g_nvls = comm.nvls_empty(max_count)
+        g_nvls.normal_(0, 1e-3)
+    elif rank == 0:
+        print("# NVLS unavailable:", getattr(comm, "nvls_error", ""))
+
     size = args.min_kb << 10
     while size <= (args.max_mb << 20):
         count = size // 4
@@ -118,6 +125,14 @@ def main():
                 roof_ms = max(wire / (NVLINK_GBS * 1e6), hbm_bytes / (hbm * 1e6))
                 rows.append({"impl": f"{algo}/{codec}", "bytes": size, "ms": ms, "wire_bytes": wire,
                              "roofline_ms": roof_ms, "roofline_frac": roof_ms / ms})
+        if g_nvls is not None and count % 512 == 0:
+            gn = g_nvls[:count]
+            ms = timed(lambda: comm.allreduce_nvls(gn, wv, 0.1, sv), iters)
+            wire = size * 1.0          # ~S per direction: ld_reduce pulls (N-1)/N*S, multimem.st pushes S/N
+            hbm_bytes = size * 3.5
+            roof_ms = max(wire / (NVLINK_GBS * 1e6), hbm_bytes / (hbm * 1e6))
+            rows.append({"impl": "nvls/f32", "bytes": size, "ms": ms, "wire_bytes": wire, "roofline_ms": roof_ms,
+                         "roofline_frac": roof_ms / ms})
         size *= 4
     for r in rows:
         if "ms" in r:

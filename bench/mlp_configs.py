@@ -1,0 +1,114 @@
+"""BASELINE.json configs 4 and 5 (run under torchrun, one rank per GPU):
+
+  deep  8 x 8192 hidden, bf16 GEMMs, MXFP8 gradient compression, per-layer bucket overlap
+  wide 16 x 16384 hidden, bf16 GEMMs, BFP gradient compression, weak scaling; reports the exposed
+        communication time per step and the accuracy of the BFP all-reduce against an fp32 one.
+
+For every config: step time with the compressed codec, with uncompressed fp32 and (optionally) with
+the PyTorch DDP baseline.  "Exposed communication" = step time at N ranks - step time of the same
+per-rank work with the all-reduce made local (comm_ctas unchanged, world 1 is run separately and
+passed in with --t1-ms, or measured here when WORLD_SIZE == 1).
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 ... bench/mlp_configs.py --config wide --out gpurun_out/wide_n8.json
+"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer  # noqa: E402
+from fpga_ai_nic_b200.ops import kernels as K  # noqa: E402
+
+CONFIGS = {
+    "reference": dict(layers=10, width=2048, mb=1792, codec="bfp"),
+    "deep": dict(layers=8, width=8192, mb=1792, codec="mxfp8"),
+    "wide": dict(layers=16, width=16384, mb=1792, codec="bfp"),
+}
+
+
+def timed(tr, x, y, steps, warmup, world):
+    for _ in range(warmup):
+        tr.step(x, y)
+    tr.wait()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        tr.step(x, y)
+    tr.wait()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / steps], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", default="deep", choices=list(CONFIGS))
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--t1-ms", type=float, default=0.0, help="step time of the same config at world 1")
+    ap.add_argument("--out", default="")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    c = CONFIGS[a.config]
+    res = {"config": a.config, "world": world, **c}
+    gen = torch.Generator().manual_seed(99 + rank)
+    x = K.cast_bf16((torch.rand(c["mb"], c["width"], generator=gen) * 0.1 - 0.05).cuda())
+    y = torch.randint(0, c["width"], (c["mb"],), generator=gen, dtype=torch.int32).cuda()
+    finals = {}
+    for codec in ([c["codec"], "f32"] if world > 1 else ["f32"]):
+        cfg = MLPConfig.reference(c["layers"], c["width"], c["mb"])
+        cfg.codec = codec
+        cfg.lr = 0.5
+        tr = MLPTrainer(cfg)
+        ms = timed(tr, x, y, a.steps, a.warmup, world)
+        res[f"ms_per_step_{codec}"] = ms
+        res[f"samples_per_s_{codec}"] = c["mb"] * world / (ms / 1e3)
+        res[f"tflops_per_gpu_{codec}"] = cfg.flops_per_step(c["mb"]) / (ms / 1e3) / 1e12
+        ctr = tr.comm.counters()
+        res[f"comm_busy_ms_per_step_{codec}"] = ctr["busy_ns"] / 1e6 / (a.steps + a.warmup)
+        res[f"comm_wait_ms_per_step_{codec}"] = ctr["wait_ns"] / 1e6 / (a.steps + a.warmup)
+        res[f"timeouts_{codec}"] = ctr["timeouts"]
+        # accuracy: the same number of identical steps under both codecs -> compare the last layer's weights
+        finals[codec] = tr.buffer("weight", c["layers"] - 1).clone()
+        tr.close()
+        tr.comm.close()
+        del tr
+        torch.cuda.empty_cache()
+    if len(finals) == 2:
+        wf, wc = finals["f32"], finals[c["codec"]]
+        cfg0 = MLPConfig.reference(c["layers"], c["width"], c["mb"])
+        res["weight_rel_l2_err_vs_fp32_allreduce"] = ((wc - wf).norm() / wf.norm()).item()
+        res["weight_max_abs_err_vs_fp32_allreduce"] = (wc - wf).abs().max().item()
+        del cfg0
+    if a.t1_ms > 0 or world == 1:
+        t1 = a.t1_ms if a.t1_ms > 0 else res["ms_per_step_f32"]
+        for codec in ([c["codec"], "f32"] if world > 1 else []):
+            res[f"exposed_comm_ms_{codec}"] = res[f"ms_per_step_{codec}"] - t1
+            res[f"weak_scaling_eff_{codec}"] = t1 / res[f"ms_per_step_{codec}"]
+    if rank == 0:
+        print(json.dumps(res), flush=True)
+        if a.out:
+            os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)
+            json.dump(res, open(a.out, "w"), indent=1)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

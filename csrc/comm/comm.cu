@@ -187,7 +187,7 @@ static int default_ctas(int algo, int nranks, size_t count) {
   const size_t frames = bfp_frames(count);
   size_t work = frames;  // frames per rank per phase
   if (algo == AINIC_ALGO_RING) work = (frames + (size_t)nranks * kSliceFrames - 1) / ((size_t)nranks * kSliceFrames);
-  else work = (frames + 31) / 32;  // 16 warps per CTA, at least two frames per warp
+  else work = (frames + 15) / 16;  // 8 warps per CTA, at least two frames per warp
   size_t ctas = work < 1 ? 1 : work;
   // The kernels are memory/latency bound: a 16 MiB bucket on 64 CTAs took ~70 us, the same bytes on
   // every SM ~15 us.  Run wide and short; the trainer can narrow it with AINIC_COMM_CTAS.
@@ -224,6 +224,8 @@ static int ensure_staging(ainic_comm* c, size_t count) {
   return AINIC_OK;
 }
 
+extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_allreduce_args_t* a);
+
 extern "C" int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args_t* a, void* stream) {
   if (!c || !a || !a->grad || a->count == 0) return AINIC_ERR_ARG;
   if (!c->connected) { set_error("communicator not connected"); return AINIC_ERR_ARG; }
@@ -243,6 +245,26 @@ extern "C" int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args
   if (algo == AINIC_ALGO_RING && check_ring_limits(c->nranks, a->count, ctas)) { set_error("ring: too many blocks per CTA"); return AINIC_ERR_ARG; }
 
   RankCtx ctx{};
+  rc = ainic_comm_fill_ctx_(c, &ctx, a);
+  if (rc) return rc;
+  // One-/two-shot run with 8-warp CTAs: 256 threads x <= 128 registers leave room for a persistent
+  // GEMM CTA (192 threads, ~215 KB smem, ~15 K registers) on the same SM, so the all-reduce
+  // overlaps the backward GEMMs instead of evicting them while it waits for peers.  The ring keeps
+  // 16 warps (one warp per frame of an 8192-value slice).
+  const int threads = algo == AINIC_ALGO_RING ? kCommThreads : kCommThreadsOverlap;
+  kern<<<ctas, threads, 0, (cudaStream_t)stream>>>(ctx);
+  CUDA_TRY(cudaGetLastError());
+  return AINIC_OK;
+}
+
+// Everything of a RankCtx that belongs to the communicator (peer tables, flags, staging, epoch).
+// Consumes one epoch: call exactly once per fused launch, in the same order on every rank.
+extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_allreduce_args_t* a) {
+  if (!c || !out || !a) return AINIC_ERR_ARG;
+  if (!c->connected) { set_error("communicator not connected"); return AINIC_ERR_ARG; }
+  int rc = ensure_staging(c, a->count);
+  if (rc) return rc;
+  RankCtx& ctx = *out;
   ctx.rank = c->rank;
   ctx.nranks = c->nranks;
   ctx.grad = a->grad;
@@ -264,10 +286,9 @@ extern "C" int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args
   ctx.epoch = ++c->epoch;
   ctx.parity = (c->parity ^= 1u);
   ctx.timeout_ns = c->timeout_ns;
-  kern<<<ctas, kCommThreads, 0, (cudaStream_t)stream>>>(ctx);
-  CUDA_TRY(cudaGetLastError());
   return AINIC_OK;
 }
+extern "C" void ainic_set_error_(const char* msg) { set_error(msg ? msg : ""); }
 
 // ---------------------------------------------------------------------------------------- emulation
 extern "C" int ainic_allreduce_emulate(int nranks, float* grads, float* weights, void* weights_bf16, float* grads_out,

@@ -177,6 +177,35 @@ inline int make_tmap(CUtensorMap* map, const void* base, uint64_t rows, uint64_t
   return r == CUDA_SUCCESS ? AINIC_OK : AINIC_ERR_CUDA;
 }
 
+// Encoding a tensor map costs a driver call (~1-2 us); a training step re-uses the same ~60 maps
+// every iteration, so keep them (direct-mapped by a hash of the key; collisions just re-encode).
+struct TmapKey {
+  const void* base;
+  uint64_t rows, cols, ld;
+  uint32_t box_c, box_r;
+  bool operator==(const TmapKey& o) const {
+    return base == o.base && rows == o.rows && cols == o.cols && ld == o.ld && box_c == o.box_c && box_r == o.box_r;
+  }
+};
+inline int cached_tmap(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_c,
+                       uint32_t box_r) {
+  constexpr int kSlots = 256;
+  struct Slot { TmapKey key; CUtensorMap map; bool valid; };
+  static thread_local Slot slots[kSlots];
+  const TmapKey key{base, rows, cols, ld, box_c, box_r};
+  uint64_t h = reinterpret_cast<uint64_t>(base) >> 8;
+  h ^= rows * 0x9E3779B97F4A7C15ull ^ cols * 0xC2B2AE3D27D4EB4Full ^ (uint64_t)box_r * 0x165667B19E3779F9ull ^ ld << 17 ^ box_c;
+  Slot& s = slots[(h ^ (h >> 29)) % kSlots];
+  if (!(s.valid && s.key == key)) {
+    const int rc = make_tmap(&s.map, base, rows, cols, ld, box_c, box_r);
+    if (rc) { s.valid = false; return rc; }
+    s.key = key;
+    s.valid = true;
+  }
+  *out = s.map;
+  return AINIC_OK;
+}
+
 inline int num_sms() {
   static int n = 0;
   if (!n) {

@@ -174,11 +174,11 @@ static int launch(const void* a, int lda, const void* b, int ldb, const EpiParam
   CUtensorMap ta, tb;
   int rc;
   // A: K-major -> global [M][K]; MN-major -> global [K][M].
-  if (A_MN) rc = make_tmap(&ta, a, ep.K, ep.M, lda, 64, BLOCK_K);
-  else rc = make_tmap(&ta, a, ep.M, ep.K, lda, BLOCK_K, BLOCK_M);
+  if (A_MN) rc = cached_tmap(&ta, a, ep.K, ep.M, lda, 64, BLOCK_K);
+  else rc = cached_tmap(&ta, a, ep.M, ep.K, lda, BLOCK_K, BLOCK_M);
   if (rc) return rc;
-  if (B_MN) rc = make_tmap(&tb, b, ep.K, ep.N, ldb, 64, BLOCK_K);
-  else rc = make_tmap(&tb, b, ep.N, ep.K, ldb, BLOCK_K, BLOCK_N);
+  if (B_MN) rc = cached_tmap(&tb, b, ep.K, ep.N, ldb, 64, BLOCK_K);
+  else rc = cached_tmap(&tb, b, ep.N, ep.K, ldb, BLOCK_K, BLOCK_N);
   if (rc) return rc;
   auto kern = gemm_kernel<BLOCK_N, A_MN, B_MN, OUT_F32>;
   constexpr int smem = num_stages(BLOCK_N) * stage_bytes(BLOCK_N) + 1024 + 256;

@@ -177,11 +177,11 @@ static int launch2(const void* a, int lda, const void* b, int ldb, const EpiPara
   constexpr int HALF_N = BLOCK_N / 2;
   CUtensorMap ta, tb;
   int rc;
-  if (A_MN) rc = make_tmap(&ta, a, ep.K, ep.M, lda, 64, BLOCK_K);
-  else rc = make_tmap(&ta, a, ep.M, ep.K, lda, BLOCK_K, BLOCK_M);
+  if (A_MN) rc = cached_tmap(&ta, a, ep.K, ep.M, lda, 64, BLOCK_K);
+  else rc = cached_tmap(&ta, a, ep.M, ep.K, lda, BLOCK_K, BLOCK_M);
   if (rc) return rc;
-  if (B_MN) rc = make_tmap(&tb, b, ep.K, ep.N, ldb, 64, BLOCK_K);
-  else rc = make_tmap(&tb, b, ep.N, ep.K, ldb, BLOCK_K, HALF_N);
+  if (B_MN) rc = cached_tmap(&tb, b, ep.K, ep.N, ldb, 64, BLOCK_K);
+  else rc = cached_tmap(&tb, b, ep.N, ep.K, ldb, BLOCK_K, HALF_N);
   if (rc) return rc;
   auto kern = gemm2_kernel<BLOCK_N, A_MN, B_MN, OUT_F32>;
   constexpr int smem = num_stages2(BLOCK_N) * stage_bytes2(BLOCK_N) + 1024 + 256;

@@ -139,6 +139,16 @@ def cuda() -> C.CDLL:
     lib.ainic_comm_counters.argtypes = [vp, c_u64p]
     lib.ainic_allreduce_fused.argtypes = [vp, C.POINTER(AllreduceArgs), vp]
     lib.ainic_allreduce_emulate.argtypes = [C.c_int, vp, vp, vp, vp, sz, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+    lib.ainic_nvls_supported.restype = C.c_int
+    lib.ainic_nvls_stage1.argtypes = [C.POINTER(vp), C.c_int, C.c_int, sz, C.c_char_p]
+    lib.ainic_nvls_stage2.argtypes = [vp]
+    lib.ainic_nvls_stage3.argtypes = [vp]
+    lib.ainic_nvls_alloc.restype = vp
+    lib.ainic_nvls_alloc.argtypes = [vp, sz]
+    lib.ainic_nvls_mc_ptr.restype = vp
+    lib.ainic_nvls_mc_ptr.argtypes = [vp, vp]
+    lib.ainic_nvls_destroy.argtypes = [vp]
+    lib.ainic_allreduce_nvls.argtypes = [vp, vp, C.POINTER(AllreduceArgs), vp]
     lib.ainic_allreduce_emulate_noalloc.argtypes = [C.c_int, vp, vp, vp, vp, sz, C.c_float, C.c_int, C.c_int, C.c_int,
                                                     C.c_int, vp, C.c_char_p, sz]
     lib.ainic_mlp_create.argtypes = [C.POINTER(vp), vp, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_float,

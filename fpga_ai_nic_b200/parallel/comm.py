@@ -90,6 +90,65 @@ class Communicator:
         N.check(self.lib.ainic_allreduce_fused(self.handle, C.byref(a), N.stream_ptr(stream)), "allreduce_fused")
         K._count()
 
+    # -- NVLS (in-switch reduce + multicast) -------------------------------------------------------
+    def enable_nvls(self, heap_bytes: int, group=None) -> bool:
+        """Create the multicast-bound heap.  Collective.  Returns False (with ``nvls_error`` set) when the
+        box does not expose NVLS; the P2P algorithms keep working either way."""
+        import torch.distributed as dist
+        self.nvls = None
+        self.nvls_error = ""
+        if self.world_size < 2:
+            self.nvls_error = "single rank"
+            return False
+        sup = torch.tensor([int(self.lib.ainic_nvls_supported())], device=self.device)
+        dist.all_reduce(sup, op=dist.ReduceOp.MIN, group=group)
+        if int(sup.item()) == 0:
+            self.nvls_error = "CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED is 0 (or the driver lacks cuMulticast*)"
+            return False
+        name = f"ainic_nvls_{os.environ.get('MASTER_PORT', '0')}_{os.getppid()}".encode()
+        h = C.c_void_p()
+        rc = self.lib.ainic_nvls_stage1(C.byref(h), self.rank, self.world_size, heap_bytes, name)
+        ok = torch.tensor([1 if rc == 0 else 0], device=self.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        if rc != 0:
+            self.nvls_error = self.lib.ainic_last_error().decode()
+        if int(ok.item()) == 0:
+            if rc == 0:
+                self.lib.ainic_nvls_destroy(h)
+                self.nvls_error = "a peer rank could not set up NVLS"
+            return False
+        for stage in (self.lib.ainic_nvls_stage2, self.lib.ainic_nvls_stage3):
+            rc = stage(h)
+            ok = torch.tensor([1 if rc == 0 else 0], device=self.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)   # doubles as the barrier between stages
+            if int(ok.item()) == 0:
+                self.nvls_error = self.lib.ainic_last_error().decode() or "a peer rank failed"
+                return False
+        self.nvls = h
+        return True
+
+    def nvls_empty(self, shape, dtype=torch.float32) -> torch.Tensor:
+        """A tensor inside the NVLS heap (same allocation order on every rank)."""
+        if isinstance(shape, int):
+            shape = (shape,)
+        nbytes = torch.tensor([], dtype=dtype).element_size()
+        for s in shape:
+            nbytes *= int(s)
+        p = self.lib.ainic_nvls_alloc(self.nvls, nbytes)
+        if not p:
+            raise N.NativeError("NVLS heap exhausted")
+        return tensor_from_ptr(p, shape, dtype, owner=self, device=self.device)
+
+    def allreduce_nvls(self, grad: torch.Tensor, weight: torch.Tensor | None = None, lr: float = 0.0,
+                       weight_bf16: torch.Tensor | None = None, grad_out: torch.Tensor | None = None, max_ctas: int = 0,
+                       stream=None) -> None:
+        a = N.AllreduceArgs(grad.data_ptr(), weight.data_ptr() if weight is not None else None,
+                            weight_bf16.data_ptr() if weight_bf16 is not None else None,
+                            grad_out.data_ptr() if grad_out is not None else None, grad.numel(), lr, K.CODEC_F32, 0,
+                            K.ALGO_NVLS, max_ctas)
+        N.check(self.lib.ainic_allreduce_nvls(self.handle, self.nvls, C.byref(a), N.stream_ptr(stream)), "allreduce_nvls")
+        K._count()
+
     def counters(self) -> dict:
         out = (C.c_uint64 * 8)()
         N.check(self.lib.ainic_comm_counters(self.handle, out), "comm_counters")

@@ -118,6 +118,24 @@ int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args_t* args, v
  * stall_* (hw/all_reduce.sv:92-98, :892-1072). */
 int ainic_comm_counters(ainic_comm_t* c, uint64_t out[8]);
 
+/* ---------------------------------------------------------------- NVLS: in-switch reduce + multicast (K13)
+ * A second, VMM-backed heap whose memory is bound to an NVSwitch multicast object.  Gradient
+ * buckets allocated from it can be reduced with multimem.ld_reduce / multimem.st
+ * (ainic_allreduce_nvls: uncompressed fp32, count % 512 == 0).  Set-up is three collective stages
+ * with a barrier (provided by the caller) between them; any failure returns
+ * AINIC_ERR_UNSUPPORTED with the reason in ainic_last_error() and the P2P kernels remain usable.
+ * The reference has no counterpart (its switch is plain Ethernet); the work it replaces is the
+ * ring of hw/all_reduce.sv:891-1086. */
+typedef struct ainic_nvls ainic_nvls_t;
+int ainic_nvls_supported(void);
+int ainic_nvls_stage1(ainic_nvls_t** out, int rank, int nranks, size_t bytes, const char* sock_name);
+int ainic_nvls_stage2(ainic_nvls_t* h);
+int ainic_nvls_stage3(ainic_nvls_t* h);
+void* ainic_nvls_alloc(ainic_nvls_t* h, size_t bytes);
+void* ainic_nvls_mc_ptr(ainic_nvls_t* h, const void* uc_ptr);
+int ainic_nvls_destroy(ainic_nvls_t* h);
+int ainic_allreduce_nvls(ainic_comm_t* c, ainic_nvls_t* h, const ainic_allreduce_args_t* args, void* stream);
+
 /* Single-GPU emulation of an N-rank all-reduce: all ranks' buffers live on one device and one
  * cooperative launch runs every rank's CTAs (the software analogue of the withheld 3-instance RTL
  * testbench, readme.pdf p.2-5).  grads/weights: [nranks][count]. */

@@ -90,6 +90,42 @@ for count in (8192 * 5 + 777, 1 << 20):
         if world > 1:
             dist.barrier()
 
+# ------------------------------------------------------------------ 1b. NVLS (multimem) all-reduce + SGD
+if world > 1:
+    have = comm.enable_nvls(64 << 20)
+    if not have:
+        say(check="nvls", ok=True, available=False, reason=comm.nvls_error)
+    else:
+        count = 1 << 20
+        gn = comm.nvls_empty(count)
+        gen = torch.Generator().manual_seed(500 + rank)
+        g = torch.randn(count, generator=gen) * 1e-3
+        w0 = torch.randn(count, generator=torch.Generator().manual_seed(8))
+        ok = True
+        for rep in range(3):
+            gn.copy_(g)
+            wv = w_heap[:count]
+            wv.copy_(w0)
+            all_g = gather(gn)
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm.allreduce_nvls(gn, wv, 0.1, sh[:count])
+            torch.cuda.synchronize()
+            exact = all_g.double().sum(0).float()
+            # the switch's summation order is not specified: compare with tolerance, replicas must agree
+            w_want = O.sgd(w0, exact, 0.1)
+            err = (wv.cpu() - w_want).abs().max().item()
+            allw = gather(wv)
+            ident = all(torch.equal(allw[r], allw[0]) for r in range(world))
+            sums = gather(gn)
+            ident &= all(torch.equal(sums[r], sums[0]) for r in range(world))
+            ok &= err < 1e-6 and ident
+        ok = all_ok(ok)
+        ctr = comm.counters()
+        say(check="nvls", ok=ok, available=True, max_err=err, identical=ident, timeouts=ctr["timeouts"], last_us=ctr["last_ns"] / 1e3)
+        if not ok or ctr["timeouts"]:
+            fails.append(("nvls",))
+
 # ------------------------------------------------------------------ 2. NIC command interface, GPU backend
 nic = Nic("gpu", comm=comm, rank=rank, nranks=world)
 count = 1 << 16
