@@ -112,7 +112,7 @@ static void fake_execute(ainic_nic* nic, const Cmd& c) {
   for (int r = 0; r < N; ++r) memcpy(all.data() + (size_t)r * c.count, F.posted[r].buf, c.count * sizeof(float));
   if (!F.barrier()) return;                 // everyone has copied the inputs; buffers may be overwritten
   int algo = nic->algo;
-  if (algo == AINIC_ALGO_AUTO) algo = c.count * 4 <= (512u << 10) ? AINIC_ALGO_ONESHOT : AINIC_ALGO_TWOSHOT;
+  if (algo == AINIC_ALGO_AUTO) algo = (N <= 2 || c.count * 4 <= (512u << 10)) ? AINIC_ALGO_ONESHOT : AINIC_ALGO_TWOSHOT;
   if (nic->codec == AINIC_CODEC_F32 && algo != AINIC_ALGO_RING) ainic_ref_allreduce_exact(all.data(), N, c.count, out.data());
   else if (algo == AINIC_ALGO_RING) ainic_ref_allreduce_ring(all.data(), N, c.count, nic->codec == AINIC_CODEC_BFP, nic->bfp_mode, out.data());
   else if (algo == AINIC_ALGO_ONESHOT) ainic_ref_allreduce_oneshot(all.data(), N, c.count, nic->codec, nic->bfp_mode, out.data());

@@ -65,6 +65,9 @@ __device__ __forceinline__ bool spin_until(const uint32_t* f, uint32_t target, u
   unsigned long long t0 = 0;
   uint32_t polls = 0;
   while ((int)(ptx::ld_acquire_sys(f) - target) < 0) {
+    // Back off: this CTA shares its SM with a GEMM CTA whose single TMA-producer and MMA-issuer
+    // threads must not lose issue slots to a tight polling loop.
+    if (polls > 2) __nanosleep(polls > 64 ? 256 : 64);
     if ((++polls & 0x3FFu) == 0) {
       const unsigned long long now = ptx::globaltimer_ns();
       if (t0 == 0) t0 = now;
@@ -170,20 +173,140 @@ __device__ __forceinline__ void reduce_tail_f32(const RankCtx& c, size_t f, floa
   }
 }
 
+// ------------------------------------------------------------------------------------------ two frames per iteration
+// The per-frame work is a chain of dependent memory operations (peer load ~2-3 us over NVLink ->
+// decode -> weight load -> store), and an 8-warp CTA has little thread-level parallelism to hide it
+// (measured: 49 us for a 16 MiB bucket at 2 ranks, ~4x the HBM time).  The hot loops therefore
+// handle TWO full frames per warp iteration and issue the loads of both before consuming either.
+// Only the last frame of a bucket can be partial (count % 512 != 0); it is kept out of the hot
+// loops and handled once per phase by the warp that owns it, through the predicated slow path.
+__device__ __forceinline__ bool frame_full(const RankCtx& c, size_t f) { return (f + 1) * kFrameVals <= c.count; }
+
+// Where frame f of rank p is read from in a reduce phase.
+template <int CODEC, int MODE>
+__device__ __forceinline__ const uint8_t* reduce_src(const RankCtx& c, size_t parity_off, int p, size_t f) {
+  return CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f * 2048
+                    : c.stage_c[p] + parity_off + f * FrameCodec<CODEC, MODE>::kBytes;
+}
+
+// acc0/acc1 = sum over ranks (rank order) of frames f0/f1; frame 1 is skipped when !has1 (warp-uniform).
+template <int CODEC, int MODE>
+__device__ __forceinline__ void reduce_pair(const RankCtx& c, size_t parity_off, size_t f0, size_t f1, bool has1,
+                                            float (&acc0)[16], float (&acc1)[16], int lane) {
+  using FC = FrameCodec<CODEC, MODE>;
+  constexpr int PB = sizeof(typename FC::Raw) > 32 ? 1 : 4;  // peers per batch: bounded by registers
+  const int N = c.nranks;
+  float v[16];
+#pragma unroll 1
+  for (int p0 = 0; p0 < N; p0 += PB) {
+    typename FC::Raw r0[PB], r1[PB];
+#pragma unroll
+    for (int k = 0; k < PB; ++k)
+      if (p0 + k < N) {
+        FC::load(reduce_src<CODEC, MODE>(c, parity_off, p0 + k, f0), r0[k], lane);
+        if (has1) FC::load(reduce_src<CODEC, MODE>(c, parity_off, p0 + k, f1), r1[k], lane);
+      }
+#pragma unroll
+    for (int k = 0; k < PB; ++k)
+      if (p0 + k < N) {
+        FC::unpack(r0[k], v, lane);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc0[i] = (p0 + k == 0) ? v[i] : acc0[i] + v[i];
+        if (has1) {
+          FC::unpack(r1[k], v, lane);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) acc1[i] = (p0 + k == 0) ? v[i] : acc1[i] + v[i];
+        }
+      }
+  }
+}
+
+// w = fmaf(-lr, g, w) (+ shadow, + reduced-gradient output) on one or two FULL frames; both weight
+// frames are loaded before either is updated.
+__device__ __forceinline__ void apply_pair(const RankCtx& c, size_t f0, size_t f1, bool has1, const float (&g0)[16],
+                                           const float (&g1)[16], int lane) {
+  if (c.grad_out) {
+    frame_store_f32(c.grad_out + f0 * kFrameVals, kFrameVals, g0, lane);
+    if (has1) frame_store_f32(c.grad_out + f1 * kFrameVals, kFrameVals, g1, lane);
+  }
+  if (c.weight) {
+    float w0[16], w1[16];
+    frame_load_f32(c.weight + f0 * kFrameVals, kFrameVals, w0, lane);
+    if (has1) frame_load_f32(c.weight + f1 * kFrameVals, kFrameVals, w1, lane);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w0[i] = fmaf(-c.lr, g0[i], w0[i]);
+    frame_store_f32(c.weight + f0 * kFrameVals, kFrameVals, w0, lane);
+    if (c.wshadow) frame_store_bf16(c.wshadow + f0 * kFrameVals, kFrameVals, w0, lane);
+    if (has1) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) w1[i] = fmaf(-c.lr, g1[i], w1[i]);
+      frame_store_f32(c.weight + f1 * kFrameVals, kFrameVals, w1, lane);
+      if (c.wshadow) frame_store_bf16(c.wshadow + f1 * kFrameVals, kFrameVals, w1, lane);
+    }
+  }
+}
+
+// Compress up to two full frames of the local gradient into stage C.
+template <int CODEC, int MODE>
+__device__ __forceinline__ void compress_pair(const RankCtx& c, size_t parity_off, size_t f0, size_t f1, bool has1, int lane) {
+  using FC = FrameCodec<CODEC, MODE>;
+  uint8_t* dst = c.stage_c[c.rank] + parity_off;
+  float a[16], b[16];
+  frame_load_f32(c.grad + f0 * kFrameVals, kFrameVals, a, lane);
+  if (has1) frame_load_f32(c.grad + f1 * kFrameVals, kFrameVals, b, lane);
+  FC::encode(a, dst + f0 * FC::kBytes, lane);
+  if (has1) FC::encode(b, dst + f1 * FC::kBytes, lane);
+}
+
+// ---- slow path for the one partial frame of a bucket (never inlined into the hot loops)
+template <int CODEC, int MODE>
+__device__ __noinline__ void tail_compress(const RankCtx& c, size_t parity_off, size_t f, int lane) {
+  float a[16];
+  load_grad_frame(c, f, a, lane);
+  FrameCodec<CODEC, MODE>::encode(a, c.stage_c[c.rank] + parity_off + f * FrameCodec<CODEC, MODE>::kBytes, lane);
+}
+// Reduce the partial frame over all ranks; publish it (two-shot: in place for fp32, re-encoded into
+// stage D slot j otherwise) when `publish`; apply it.
+template <int CODEC, int MODE>
+__device__ __noinline__ void tail_reduce_apply(const RankCtx& c, size_t parity_off, size_t f, bool publish, size_t j, int lane) {
+  using FC = FrameCodec<CODEC, MODE>;
+  float acc[16];
+  if (CODEC == 0) reduce_tail_f32(c, f, acc, lane);
+  else reduce_frame<CODEC, MODE>(c.nranks, [&](int p) { return reduce_src<CODEC, MODE>(c, parity_off, p, f); }, acc, lane);
+  if (publish) {
+    if (CODEC == 0) {
+      if (c.nranks > 1) frame_store_f32(c.grad + f * kFrameVals, (int)(c.count - f * kFrameVals), acc, lane);
+    } else {
+      uint8_t* dst = c.stage_d[c.rank] + j * FC::kBytes;
+      FC::encode(acc, dst, lane);
+      __syncwarp();
+      frame_decode<CODEC, MODE>(dst, acc, lane);
+    }
+  }
+  apply_frame(c, f, acc, lane);
+}
+template <int CODEC, int MODE>
+__device__ __noinline__ void tail_gather_apply(const RankCtx& c, int p, size_t f, size_t j, int lane) {
+  float g[16];
+  if (CODEC == 0) frame_load_f32(c.peer_grad[p] + f * kFrameVals, (int)(c.count - f * kFrameVals), g, lane);
+  else frame_decode<CODEC, MODE>(c.stage_d[p] + j * FrameCodec<CODEC, MODE>::kBytes, g, lane);
+  apply_frame(c, f, g, lane);
+}
+
 // ------------------------------------------------------------------------------------------ one-shot
 template <int CODEC, int MODE>
 __device__ void oneshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws) {
-  using FC = FrameCodec<CODEC, MODE>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
   const size_t frames = bfp_frames(c.count);
+  const size_t full = c.count / kFrameVals;                       // frames [0, full) are complete
   const int N = c.nranks;
   const size_t parity_off = c.parity ? c.stage_c_half : 0;
-  float v[16];
+  const size_t first = (size_t)cta + (size_t)warp * nctas, step = (size_t)nctas * wpb;
+  const bool own_tail = full < frames && (int)(full % nctas) == cta && (int)((full / nctas) % wpb) == warp;
   if (CODEC != 0) {
-    for (size_t f = (size_t)cta + (size_t)warp * nctas; f < frames; f += (size_t)nctas * wpb) {
-      load_grad_frame(c, f, v, lane);
-      FC::encode(v, c.stage_c[c.rank] + parity_off + f * FC::kBytes, lane);
-    }
+#pragma unroll 1
+    for (size_t f0 = first; f0 < full; f0 += 2 * step) compress_pair<CODEC, MODE>(c, parity_off, f0, f0 + step, f0 + step < full, lane);
+    if (own_tail) tail_compress<CODEC, MODE>(c, parity_off, full, lane);
   }
   if (N > 1) {
     signal_all(c, 0, cta, c.epoch);
@@ -191,18 +314,15 @@ __device__ void oneshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   } else {
     __syncthreads();
   }
-  for (size_t f = (size_t)cta + (size_t)warp * nctas; f < frames; f += (size_t)nctas * wpb) {
-    float acc[16];
-    if (CODEC == 0 && (f + 1) * kFrameVals > c.count) {
-      reduce_tail_f32(c, f, acc, lane);
-    } else {
-      reduce_frame<CODEC, MODE>(N, [&](int p) -> const uint8_t* {
-        return CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f * 2048
-                          : c.stage_c[p] + parity_off + f * FC::kBytes;
-      }, acc, lane);
-    }
-    apply_frame(c, f, acc, lane);
+#pragma unroll 1
+  for (size_t f0 = first; f0 < full; f0 += 2 * step) {
+    const size_t f1 = f0 + step;
+    const bool has1 = f1 < full;
+    float acc0[16], acc1[16];
+    reduce_pair<CODEC, MODE>(c, parity_off, f0, f1, has1, acc0, acc1, lane);
+    apply_pair(c, f0, f1, has1, acc0, acc1, lane);
   }
+  if (own_tail) tail_reduce_apply<CODEC, MODE>(c, parity_off, full, false, 0, lane);
   if (CODEC == 0 && N > 1) {  // peers read my gradient in place: do not return before they are done
     signal_all(c, 2, cta, c.epoch);
     wait_all(c, 2, cta, c.epoch, ws);
@@ -215,19 +335,30 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   using FC = FrameCodec<CODEC, MODE>;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
   const size_t frames = bfp_frames(c.count);
+  const size_t full = c.count / kFrameVals;
   const int N = c.nranks;
   const size_t shard = (frames + N - 1) / N;  // frames per shard
   const size_t parity_off = c.parity ? c.stage_c_half : 0;
-  float v[16];
+  const size_t first = (size_t)cta + (size_t)warp * nctas, step = (size_t)nctas * wpb;
+  // the partial frame (if any): shard ts, index tj inside it; CTA b handles the same j of every shard,
+  // so that a peer's CTA b finds exactly the frames it needs behind CTA b's flag
+  const bool has_tail = full < frames;
+  const int ts = has_tail ? (int)(full / shard) : -1;
+  const size_t tj = has_tail ? full % shard : 0;
+  const bool own_tail = has_tail && (int)(tj % nctas) == cta && (int)((tj / nctas) % wpb) == warp;
+  // number of complete frames in shard s
+  auto shard_full = [&](int s) -> size_t {
+    const size_t lo = (size_t)s * shard;
+    return full <= lo ? 0 : (full - lo < shard ? full - lo : shard);
+  };
   // phase 0: compress the whole local gradient
   if (CODEC != 0) {
-    for (int s = 0; s < N; ++s)
-      for (size_t j = (size_t)cta + (size_t)warp * nctas; j < shard; j += (size_t)nctas * wpb) {
-        const size_t f = (size_t)s * shard + j;
-        if (f >= frames) break;
-        load_grad_frame(c, f, v, lane);
-        FC::encode(v, c.stage_c[c.rank] + parity_off + f * FC::kBytes, lane);
-      }
+    for (int s = 0; s < N; ++s) {
+      const size_t base = (size_t)s * shard, lim = shard_full(s);
+#pragma unroll 1
+      for (size_t j0 = first; j0 < lim; j0 += 2 * step) compress_pair<CODEC, MODE>(c, parity_off, base + j0, base + j0 + step, j0 + step < lim, lane);
+    }
+    if (own_tail) tail_compress<CODEC, MODE>(c, parity_off, full, lane);
   }
   if (N > 1) {
     signal_all(c, 0, cta, c.epoch);
@@ -236,31 +367,35 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
     __syncthreads();
   }
   // phase 1: reduce my shard from every rank, publish it re-encoded, update my shard's weights
-  for (size_t j = (size_t)cta + (size_t)warp * nctas; j < shard; j += (size_t)nctas * wpb) {
-    const size_t f = (size_t)c.rank * shard + j;
-    if (f >= frames) break;
-    const bool tail = CODEC == 0 && (f + 1) * kFrameVals > c.count;
-    float acc[16];
-    if (tail) {
-      reduce_tail_f32(c, f, acc, lane);
-    } else {
-      reduce_frame<CODEC, MODE>(N, [&](int p) -> const uint8_t* {
-        return CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f * 2048
-                          : c.stage_c[p] + parity_off + f * FC::kBytes;
-      }, acc, lane);
-    }
-    if (CODEC == 0) {
-      if (N > 1) {  // in place: peers pull the reduced shard out of my gradient buffer
-        const size_t base = f * kFrameVals;
-        frame_store_f32(c.grad + base, tail ? (int)(c.count - base) : kFrameVals, acc, lane);
+  {
+    const size_t base = (size_t)c.rank * shard, lim = shard_full(c.rank);
+#pragma unroll 1
+    for (size_t j0 = first; j0 < lim; j0 += 2 * step) {
+      const size_t j1 = j0 + step, f0 = base + j0, f1 = base + j1;
+      const bool has1 = j1 < lim;
+      float acc0[16], acc1[16];
+      reduce_pair<CODEC, MODE>(c, parity_off, f0, f1, has1, acc0, acc1, lane);
+      if (CODEC == 0) {
+        if (N > 1) {  // in place: peers pull the reduced shard out of my gradient buffer
+          frame_store_f32(c.grad + f0 * kFrameVals, kFrameVals, acc0, lane);
+          if (has1) frame_store_f32(c.grad + f1 * kFrameVals, kFrameVals, acc1, lane);
+        }
+      } else {
+        // publish, then apply exactly what the peers will decode (fixes SURVEY D11)
+        uint8_t* d0 = c.stage_d[c.rank] + j0 * FC::kBytes;
+        uint8_t* d1 = c.stage_d[c.rank] + j1 * FC::kBytes;
+        FC::encode(acc0, d0, lane);
+        if (has1) FC::encode(acc1, d1, lane);
+        __syncwarp();
+        typename FC::Raw r0, r1;
+        FC::load(d0, r0, lane);
+        if (has1) FC::load(d1, r1, lane);
+        FC::unpack(r0, acc0, lane);
+        if (has1) FC::unpack(r1, acc1, lane);
       }
-    } else {
-      uint8_t* dst = c.stage_d[c.rank] + j * FC::kBytes;
-      FC::encode(acc, dst, lane);
-      __syncwarp();
-      frame_decode<CODEC, MODE>(dst, acc, lane);  // apply exactly what the peers will decode (fixes SURVEY D11)
+      apply_pair(c, f0, f1, has1, acc0, acc1, lane);
     }
-    apply_frame(c, f, acc, lane);
+    if (own_tail && ts == c.rank) tail_reduce_apply<CODEC, MODE>(c, parity_off, full, true, tj, lane);
   }
   if (N == 1) return;
   signal_all(c, 1, cta, c.epoch);
@@ -268,17 +403,20 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   // phase 2: pull every other rank's reduced shard
   for (int dp = 1; dp < N; ++dp) {
     const int p = (c.rank + dp) % N;  // stagger the peers so the links are used evenly
-    for (size_t j = (size_t)cta + (size_t)warp * nctas; j < shard; j += (size_t)nctas * wpb) {
-      const size_t f = (size_t)p * shard + j;
-      if (f >= frames) break;
-      if (CODEC == 0) {
-        if ((f + 1) * kFrameVals > c.count) frame_load_f32(c.peer_grad[p] + f * kFrameVals, (int)(c.count - f * kFrameVals), v, lane);
-        else frame_decode<CODEC, MODE>(reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f * 2048, v, lane);
-      } else {
-        frame_decode<CODEC, MODE>(c.stage_d[p] + j * FC::kBytes, v, lane);
-      }
-      apply_frame(c, f, v, lane);
+    const size_t base = (size_t)p * shard, lim = shard_full(p);
+#pragma unroll 1
+    for (size_t j0 = first; j0 < lim; j0 += 2 * step) {
+      const size_t j1 = j0 + step, f0 = base + j0, f1 = base + j1;
+      const bool has1 = j1 < lim;
+      typename FC::Raw r0, r1;
+      float g0[16], g1[16];
+      FC::load(CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f0 * 2048 : c.stage_d[p] + j0 * FC::kBytes, r0, lane);
+      if (has1) FC::load(CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f1 * 2048 : c.stage_d[p] + j1 * FC::kBytes, r1, lane);
+      FC::unpack(r0, g0, lane);
+      if (has1) FC::unpack(r1, g1, lane);
+      apply_pair(c, f0, f1, has1, g0, g1, lane);
     }
+    if (own_tail && ts == p) tail_gather_apply<CODEC, MODE>(c, p, full, tj, lane);
   }
   if (CODEC == 0) {
     signal_all(c, 2, cta, c.epoch);
@@ -391,9 +529,24 @@ __device__ __forceinline__ void run_rank(const RankCtx& c, int cta, int nctas) {
   }
 }
 
+// Ring: 16 warps (one per frame of a slice).  One-/two-shot: 8-warp CTAs capped at 160 registers,
+// i.e. 40 K registers per CTA, which fits beside a persistent GEMM CTA (192 threads x 80) on one SM.
+#define AINIC_COMM_RING_ATTR __launch_bounds__(kCommThreads)
+#define AINIC_COMM_OVERLAP_ATTR __maxnreg__(160)
+template <int ALGO>
+constexpr int comm_threads() { return ALGO == AINIC_ALGO_RING ? kCommThreads : kCommThreadsOverlap; }
+
 template <int ALGO, int CODEC, int MODE>
-__global__ void __launch_bounds__(kCommThreads) allreduce_kernel(const RankCtx c) {
+__global__ void AINIC_COMM_RING_ATTR allreduce_kernel(const RankCtx c) {
   run_rank<ALGO, CODEC, MODE>(c, blockIdx.x, gridDim.x);
+}
+template <int ALGO, int CODEC, int MODE>
+__global__ void AINIC_COMM_OVERLAP_ATTR allreduce_ov_kernel(const RankCtx c) {
+  run_rank<ALGO, CODEC, MODE>(c, blockIdx.x, gridDim.x);
+}
+template <int ALGO, int CODEC, int MODE>
+__global__ void AINIC_COMM_OVERLAP_ATTR allreduce_emul_ov_kernel(const RankCtx* ctxs) {
+  run_rank<ALGO, CODEC, MODE>(ctxs[blockIdx.y], blockIdx.x, gridDim.x);
 }
 // Single-GPU emulation: blockIdx.y selects the rank (cooperative launch keeps all of them resident).
 template <int ALGO, int CODEC, int MODE>

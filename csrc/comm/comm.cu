@@ -138,23 +138,35 @@ extern "C" void ainic_comm_set_timeout_ns_(ainic_comm_t* c, unsigned long long n
 typedef void (*KernFn)(const RankCtx);
 typedef void (*EmulFn)(const RankCtx*);
 
+template <int ALGO, int CODEC, int MODE>
+static KernFn kern_of() {
+  if constexpr (ALGO == AINIC_ALGO_RING) return allreduce_kernel<ALGO, CODEC, MODE>;
+  else return allreduce_ov_kernel<ALGO, CODEC, MODE>;
+}
+template <int ALGO, int CODEC, int MODE>
+static EmulFn emul_of() {
+  if constexpr (ALGO == AINIC_ALGO_RING) return allreduce_emul_kernel<ALGO, CODEC, MODE>;
+  else return allreduce_emul_ov_kernel<ALGO, CODEC, MODE>;
+}
+static int threads_for(int algo) { return algo == AINIC_ALGO_RING ? kCommThreads : kCommThreadsOverlap; }
+
 template <int ALGO>
 static KernFn pick_kernel(int codec, int mode) {
   switch (codec) {
-    case AINIC_CODEC_F32: return allreduce_kernel<ALGO, 0, 0>;
-    case AINIC_CODEC_BFP: return mode == AINIC_BFP_HW_EXACT ? allreduce_kernel<ALGO, 1, 0> : allreduce_kernel<ALGO, 1, 1>;
-    case AINIC_CODEC_MXFP8: return allreduce_kernel<ALGO, 2, 0>;
-    case AINIC_CODEC_BF16: return allreduce_kernel<ALGO, 3, 0>;
+    case AINIC_CODEC_F32: return kern_of<ALGO, 0, 0>();
+    case AINIC_CODEC_BFP: return mode == AINIC_BFP_HW_EXACT ? kern_of<ALGO, 1, 0>() : kern_of<ALGO, 1, 1>();
+    case AINIC_CODEC_MXFP8: return kern_of<ALGO, 2, 0>();
+    case AINIC_CODEC_BF16: return kern_of<ALGO, 3, 0>();
   }
   return nullptr;
 }
 template <int ALGO>
 static EmulFn pick_emul(int codec, int mode) {
   switch (codec) {
-    case AINIC_CODEC_F32: return allreduce_emul_kernel<ALGO, 0, 0>;
-    case AINIC_CODEC_BFP: return mode == AINIC_BFP_HW_EXACT ? allreduce_emul_kernel<ALGO, 1, 0> : allreduce_emul_kernel<ALGO, 1, 1>;
-    case AINIC_CODEC_MXFP8: return allreduce_emul_kernel<ALGO, 2, 0>;
-    case AINIC_CODEC_BF16: return allreduce_emul_kernel<ALGO, 3, 0>;
+    case AINIC_CODEC_F32: return emul_of<ALGO, 0, 0>();
+    case AINIC_CODEC_BFP: return mode == AINIC_BFP_HW_EXACT ? emul_of<ALGO, 1, 0>() : emul_of<ALGO, 1, 1>();
+    case AINIC_CODEC_MXFP8: return emul_of<ALGO, 2, 0>();
+    case AINIC_CODEC_BF16: return emul_of<ALGO, 3, 0>();
   }
   return nullptr;
 }
@@ -177,7 +189,10 @@ static EmulFn pick_emul(int algo, int codec, int mode) {
 
 static int resolve_algo(int algo, int nranks, size_t count) {
   if (algo != AINIC_ALGO_AUTO) return algo;
-  if (nranks == 1) return AINIC_ALGO_ONESHOT;
+  // One-shot has one barrier phase instead of two and the same wire bytes as two-shot at N = 2
+  // (measured in the trainer at 2 ranks: 0.77 vs 0.88 ms/step); beyond that its (N-1)*S traffic loses
+  // to two-shot's 2(N-1)/N*S except for small, latency-bound buckets.
+  if (nranks <= 2) return AINIC_ALGO_ONESHOT;
   return count * sizeof(float) <= (512u << 10) ? AINIC_ALGO_ONESHOT : AINIC_ALGO_TWOSHOT;
 }
 
@@ -251,8 +266,7 @@ extern "C" int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args
   // GEMM CTA (192 threads, ~215 KB smem, ~15 K registers) on the same SM, so the all-reduce
   // overlaps the backward GEMMs instead of evicting them while it waits for peers.  The ring keeps
   // 16 warps (one warp per frame of an 8192-value slice).
-  const int threads = algo == AINIC_ALGO_RING ? kCommThreads : kCommThreadsOverlap;
-  kern<<<ctas, threads, 0, (cudaStream_t)stream>>>(ctx);
+  kern<<<ctas, threads_for(algo), 0, (cudaStream_t)stream>>>(ctx);
   CUDA_TRY(cudaGetLastError());
   return AINIC_OK;
 }
@@ -303,7 +317,7 @@ extern "C" int ainic_allreduce_emulate(int nranks, float* grads, float* weights,
   int dev = 0, sms = 0, per_sm = 0;
   CUDA_TRY(cudaGetDevice(&dev));
   CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kCommThreads, 0));
+  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads_for(algo), 0));
   if ((long)ctas * nranks > (long)sms * per_sm) { set_error("emulation grid exceeds co-resident capacity"); return AINIC_ERR_ARG; }
 
   const size_t frames = bfp_frames(count);
@@ -345,7 +359,7 @@ extern "C" int ainic_allreduce_emulate(int nranks, float* grads, float* weights,
   CUDA_TRY(cudaMemcpyAsync(d_ctx, h, sizeof(RankCtx) * nranks, cudaMemcpyHostToDevice, s));
   const RankCtx* arg0 = d_ctx;
   void* args[] = {(void*)&arg0};
-  cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas, nranks), dim3(kCommThreads), args, 0, s);
+  cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas, nranks), dim3(threads_for(algo)), args, 0, s);
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   unsigned long long ctr[8] = {};
   if (e == cudaSuccess) cudaMemcpy(ctr, h[0].counters, sizeof(ctr), cudaMemcpyDeviceToHost);

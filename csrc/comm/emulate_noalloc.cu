@@ -64,10 +64,20 @@ struct EmulArgs {
   RankCtx ctx[kNaMaxRanks];
 };
 static_assert(sizeof(EmulArgs) <= 4000, "contexts must fit in kernel parameter space");
+typedef void (*ByValFnT)(const EmulArgs);
 
 template <int ALGO, int CODEC, int MODE>
-__global__ void __launch_bounds__(kCommThreads) allreduce_emul_byval_kernel(const EmulArgs args) {
+__global__ void AINIC_COMM_RING_ATTR allreduce_emul_byval_kernel(const EmulArgs args) {
   run_rank<ALGO, CODEC, MODE>(args.ctx[blockIdx.y], blockIdx.x, gridDim.x);
+}
+template <int ALGO, int CODEC, int MODE>
+__global__ void AINIC_COMM_OVERLAP_ATTR allreduce_emul_byval_ov_kernel(const EmulArgs args) {
+  run_rank<ALGO, CODEC, MODE>(args.ctx[blockIdx.y], blockIdx.x, gridDim.x);
+}
+template <int ALGO, int CODEC, int MODE>
+ByValFnT byval_of() {
+  if constexpr (ALGO == AINIC_ALGO_RING) return allreduce_emul_byval_kernel<ALGO, CODEC, MODE>;
+  else return allreduce_emul_byval_ov_kernel<ALGO, CODEC, MODE>;
 }
 
 typedef void (*ByValFn)(const EmulArgs);
@@ -75,10 +85,10 @@ typedef void (*ByValFn)(const EmulArgs);
 template <int ALGO>
 ByValFn pick_codec(int codec, int mode) {
   switch (codec) {
-    case AINIC_CODEC_F32: return allreduce_emul_byval_kernel<ALGO, 0, 0>;
-    case AINIC_CODEC_BFP: return mode == AINIC_BFP_HW_EXACT ? allreduce_emul_byval_kernel<ALGO, 1, 0> : allreduce_emul_byval_kernel<ALGO, 1, 1>;
-    case AINIC_CODEC_MXFP8: return allreduce_emul_byval_kernel<ALGO, 2, 0>;
-    case AINIC_CODEC_BF16: return allreduce_emul_byval_kernel<ALGO, 3, 0>;
+    case AINIC_CODEC_F32: return byval_of<ALGO, 0, 0>();
+    case AINIC_CODEC_BFP: return mode == AINIC_BFP_HW_EXACT ? byval_of<ALGO, 1, 0>() : byval_of<ALGO, 1, 1>();
+    case AINIC_CODEC_MXFP8: return byval_of<ALGO, 2, 0>();
+    case AINIC_CODEC_BF16: return byval_of<ALGO, 3, 0>();
   }
   return nullptr;
 }
@@ -139,7 +149,7 @@ extern "C" int ainic_allreduce_emulate_noalloc(int nranks, float* grads, float* 
       (nranks > 1 && (count & 3)))
     return fail(errbuf, errbuf_len, AINIC_ERR_ARG,
                 "no-alloc all-reduce: buffers must be 16-byte aligned and count a multiple of 4 when nranks > 1%s");
-  if (algo == AINIC_ALGO_AUTO) algo = (nranks == 1 || count * sizeof(float) <= (512u << 10)) ? AINIC_ALGO_ONESHOT : AINIC_ALGO_TWOSHOT;
+  if (algo == AINIC_ALGO_AUTO) algo = (nranks <= 2 || count * sizeof(float) <= (512u << 10)) ? AINIC_ALGO_ONESHOT : AINIC_ALGO_TWOSHOT;
   ByValFn kern = pick(algo, codec, bfp_mode);
   if (!kern) return fail(errbuf, errbuf_len, AINIC_ERR_UNSUPPORTED, "no-alloc all-reduce: unsupported algorithm/codec combination%s");
   const int ctas = ctas_per_rank > 0 ? ctas_per_rank : 4;
@@ -152,7 +162,7 @@ extern "C" int ainic_allreduce_emulate_noalloc(int nranks, float* grads, float* 
   int dev = 0, sms = 0, per_sm = 0;
   cudaGetDevice(&dev);
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kCommThreads, 0) != cudaSuccess)
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, algo == AINIC_ALGO_RING ? kCommThreads : kCommThreadsOverlap, 0) != cudaSuccess)
     return fail(errbuf, errbuf_len, AINIC_ERR_CUDA, "no-alloc all-reduce: occupancy query failed: %s", cudaGetErrorString(cudaGetLastError()));
   if ((long)ctas * nranks > (long)sms * per_sm)
     return fail(errbuf, errbuf_len, AINIC_ERR_ARG, "no-alloc all-reduce: grid would not be co-resident%s");
@@ -189,7 +199,7 @@ extern "C" int ainic_allreduce_emulate_noalloc(int nranks, float* grads, float* 
       return fail(errbuf, errbuf_len, AINIC_ERR_CUDA, "no-alloc all-reduce: clearing flags failed: %s", cudaGetErrorString(cudaGetLastError()));
   }
   void* kargs[] = {(void*)&args};
-  cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas, nranks), dim3(kCommThreads), kargs, 0, s);
+  cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas, nranks), dim3(algo == AINIC_ALGO_RING ? kCommThreads : kCommThreadsOverlap), kargs, 0, s);
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   if (e != cudaSuccess) return fail(errbuf, errbuf_len, AINIC_ERR_CUDA, "no-alloc all-reduce: launch failed: %s", cudaGetErrorString(e));
   unsigned long long ctr[8] = {};

@@ -1,0 +1,55 @@
+"""CPU checks of the host-side utilities: the reference's report format (PERFDUMP line and FLOP
+accounting, sw/mlp_mpi_example_f32.cpp:794-808), the launcher plumbing and the MLP config math."""
+import re
+import subprocess
+import sys
+
+from fpga_ai_nic_b200.models.mlp import MLPConfig
+from fpga_ai_nic_b200.parallel import launcher
+from fpga_ai_nic_b200.utils import profiling
+
+
+def test_flop_accounting_matches_reference_formula():
+    sizes = [2048] * 11
+    g = profiling.flops_reference(sizes, 5376, 1)           # 3 ranks x 1792 (sw/run.sh:16)
+    want = (9 * 6.0 + 4.0) * 5376 * 2048 * 2048 / 1e9
+    assert abs(g - want) < 1e-6 * want
+    cfg = MLPConfig.reference()
+    assert abs(cfg.flops_per_step(5376) / 1e9 - want) < 1e-6 * want
+    assert cfg.param_count() == 10 * 2048 * 2048 and cfg.nlayers == 10 and cfg.mb == 1792
+
+
+def test_perfdump_block_has_reference_shape():
+    txt = profiling.perfdump([256, 512, 128], 64, 2, 10, 0.5, {"fwd_fc": 100.0, "bwdupd_fc": 200.0, "bwdupd_first": 50.0})
+    lines = txt.splitlines()
+    assert lines[0].startswith("GFLOP  = ") and lines[1].startswith("fp time = ") and lines[2].startswith("GFLOPS  = ")
+    assert re.match(r"^PERFDUMP,BP,[^,]+,2,64,256,512,[0-9.]+,[0-9.]+$", lines[3])
+    assert any(l.startswith("Bwdupd compute FIRST time overlaped") for l in lines)
+    assert "samples/s = 2560" in txt
+
+
+def test_launcher_runs_a_script_single_process(tmp_path):
+    script = tmp_path / "hello.py"
+    script.write_text("import os; print('rank', os.environ.get('RANK', '0'))\n")
+    p = launcher.launch(1, [str(script)])
+    assert p.returncode == 0 and "rank 0" in p.stdout
+
+
+def test_launcher_two_ranks_gloo(tmp_path):
+    script = tmp_path / "two.py"
+    script.write_text(
+        "import os, sys, torch, torch.distributed as dist\n"
+        "dist.init_process_group('gloo')\n"
+        "t = torch.tensor([float(dist.get_rank() + 1)])\n"
+        "dist.all_reduce(t)\n"
+        "open(os.path.join(sys.argv[1], 'rank%d.txt' % dist.get_rank()), 'w').write(str(t.item()))\n"
+        "dist.destroy_process_group()\n")
+    p = launcher.launch(2, [str(script), str(tmp_path)], timeout=120)
+    assert p.returncode == 0, p.stderr[-2000:]
+    # results go through files: torchrun does not always forward the last lines of a worker's stdout
+    assert [(tmp_path / f"rank{r}.txt").read_text() for r in range(2)] == ["3.0", "3.0"]
+
+
+def test_bench_reference_arm_reports_unavailable():
+    p = subprocess.run([sys.executable, "bench.py", "--impl", "reference"], capture_output=True, text=True, cwd=launcher.ROOT)
+    assert p.returncode == 0 and '"impl": "reference"' in p.stdout and "unavailable" in p.stdout
