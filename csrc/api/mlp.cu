@@ -34,6 +34,7 @@ struct Layer {
   cudaEvent_t dw_ready = nullptr;   // gradient bucket complete (wgrad stream)
   cudaEvent_t updated = nullptr;    // weights + shadow updated (comm stream)
   cudaEvent_t dx_done = nullptr;    // backward-data GEMM finished reading the shadow (main stream)
+  uint8_t* cg[2] = {nullptr, nullptr};  // compressed gradient (BFP / MXFP8 frames), symmetric heap, one per step parity
 };
 
 }  // namespace
@@ -52,6 +53,8 @@ struct ainic_mlp {
   cudaEvent_t fwd_done = nullptr;
   bool first_step = true;
   unsigned long long launches = 0;
+  unsigned long long step_idx = 0;
+  bool fuse_compress = false;        // weight-gradient GEMM epilogue emits the wire format directly
 };
 
 static int fail(const char* what) {
@@ -79,6 +82,14 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
   if (const char* e = getenv("AINIC_COMM_CTAS")) m->comm_ctas = atoi(e);
   if (const char* e = getenv("AINIC_GEMM_CTAS")) m->gemm_ctas = atoi(e);
   if (const char* e = getenv("AINIC_WGRAD_CTAS")) m->wgrad_ctas = atoi(e);
+  // With more than one rank and a block-compressed wire format the weight-gradient GEMM writes the
+  // wire format itself (the reference's BFP adapter sits right behind the adder tree the same way,
+  // hw/all_reduce.sv:745-772): no fp32 gradient in memory, no compression pass in the all-reduce.
+  // Opt-in (AINIC_FUSE_COMPRESS=1): it takes ~10 us off every all-reduce call but the quantisation
+  // lengthens the GEMM's exposed epilogue, which at 2 ranks costs more than it saves (0.80 vs 0.77
+  // ms/step); it pays when the all-reduce queue, not the GEMM chain, is the critical path.
+  m->fuse_compress = ainic_comm_size(comm) > 1 && (codec == AINIC_CODEC_BFP || codec == AINIC_CODEC_MXFP8) &&
+                     getenv("AINIC_FUSE_COMPRESS") && atoi(getenv("AINIC_FUSE_COMPRESS")) == 1;
   m->layers.resize(nlayers);
   m->act.resize(nlayers + 1);
   m->dact.resize(nlayers + 1);
@@ -100,6 +111,12 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
     const size_t n = (size_t)L.in * L.out;
     L.w = static_cast<float*>(ainic_comm_alloc(comm, n * 4, 4096));
     L.g = static_cast<float*>(ainic_comm_alloc(comm, n * 4, 4096));
+    if (m->fuse_compress && n % 512 == 0 && L.in % 32 == 0) {
+      const size_t cbytes = codec == AINIC_CODEC_BFP ? ainic_bfp_bytes(n) : ainic_mx_bytes(n);
+      L.cg[0] = static_cast<uint8_t*>(ainic_comm_alloc(comm, cbytes, 4096));
+      L.cg[1] = static_cast<uint8_t*>(ainic_comm_alloc(comm, cbytes, 4096));
+      if (!L.cg[0] || !L.cg[1]) return AINIC_ERR_ARG;
+    }
     if (!L.w || !L.g) return AINIC_ERR_ARG;
     TRY_CUDA(cudaMalloc(&L.wb, n * 2));
     TRY_CUDA(cudaMalloc(&L.bias, (size_t)L.out * 4));
@@ -214,8 +231,14 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
     TRY_CUDA(cudaStreamWaitEvent(m->wgrad_stream, L.dy_ready, 0));
     ainic_gemm_epilogue_t we{};
     we.alpha = 1.0f;
-    TRY(ainic_gemm_bf16(AINIC_GEMM_TN, m->dact[l + 1], L.out, m->act[l], L.in, L.g, L.in, L.out, L.in, m->mb, &we, 0,
-                        m->wgrad_ctas, m->wgrad_stream));
+    uint8_t* cg = L.cg[m->step_idx & 1];   // null unless the epilogue emits the wire format
+    if (cg) {
+      we.cgrad = cg;
+      we.codec = m->codec;
+      we.bfp_mode = m->bfp_mode;
+    }
+    TRY(ainic_gemm_bf16(AINIC_GEMM_TN, m->dact[l + 1], L.out, m->act[l], L.in, cg ? nullptr : L.g, L.in, L.out, L.in,
+                        m->mb, &we, 0, m->wgrad_ctas, m->wgrad_stream));
     m->launches++;
     if (use_bias) {
       TRY(ainic_bias_grad(m->dact[l + 1], L.dbias, m->mb, L.out, L.out, m->wgrad_stream));
@@ -245,11 +268,13 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
     a.bfp_mode = m->bfp_mode;
     a.algo = m->algo;
     a.max_ctas = m->comm_ctas;
+    a.grad_compressed = cg;
     TRY(ainic_allreduce_fused(m->comm, &a, m->comm_stream));
     m->launches++;
     TRY_CUDA(cudaEventRecord(L.updated, m->comm_stream));
   }
   m->first_step = false;
+  m->step_idx++;
   return AINIC_OK;
 }
 

@@ -36,7 +36,8 @@ constexpr int kCommThreadsOverlap = 256;   // one-/two-shot/NVLS: small enough t
 constexpr int kSliceFrames = 16;           // BUF_SIZE = 512 cache lines = 8192 fp32 (hw/all_reduce.sv:102-103)
 constexpr int kNumCounters = 8;
 
-enum { CTR_BUSY_NS = 0, CTR_WAIT_NS = 1, CTR_LAUNCHES = 2, CTR_TIMEOUTS = 3, CTR_TICKET = 4, CTR_LAST_NS = 5 };
+enum { CTR_BUSY_NS = 0, CTR_WAIT_NS = 1, CTR_LAUNCHES = 2, CTR_TIMEOUTS = 3, CTR_TICKET = 4, CTR_LAST_NS = 5,
+       CTR_TO_BARRIER0_NS = 6, CTR_TO_BARRIER1_NS = 7 };
 
 struct RankCtx {
   int rank, nranks;
@@ -55,6 +56,7 @@ struct RankCtx {
   float lr;
   uint32_t epoch;                // increments on every fused call (all ranks issue the same sequence)
   uint32_t parity;               // which half of stage_c this call writes (toggles per staging call)
+  uint32_t precompressed;        // stage_c already holds this rank's encoded gradient (GEMM epilogue wrote it)
   unsigned long long timeout_ns;
 };
 
@@ -79,8 +81,12 @@ __device__ __forceinline__ bool spin_until(const uint32_t* f, uint32_t target, u
 
 struct WaitStats {
   unsigned long long wait_ns;
+  unsigned long long mark[2];  // %globaltimer after the first / second cross-rank barrier (CTA 0 reports them)
   uint32_t timeouts;
 };
+__device__ __forceinline__ void mark_phase(WaitStats& ws, int i) {
+  if (threadIdx.x == 0) ws.mark[i] = ptx::globaltimer_ns();
+}
 
 // All stores of this CTA issued before the call become visible to every peer that observes the flag.
 __device__ __forceinline__ void signal_all(const RankCtx& c, int phase, int cta, uint32_t value) {
@@ -303,7 +309,7 @@ __device__ void oneshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   const size_t parity_off = c.parity ? c.stage_c_half : 0;
   const size_t first = (size_t)cta + (size_t)warp * nctas, step = (size_t)nctas * wpb;
   const bool own_tail = full < frames && (int)(full % nctas) == cta && (int)((full / nctas) % wpb) == warp;
-  if (CODEC != 0) {
+  if (CODEC != 0 && !c.precompressed) {
 #pragma unroll 1
     for (size_t f0 = first; f0 < full; f0 += 2 * step) compress_pair<CODEC, MODE>(c, parity_off, f0, f0 + step, f0 + step < full, lane);
     if (own_tail) tail_compress<CODEC, MODE>(c, parity_off, full, lane);
@@ -314,6 +320,7 @@ __device__ void oneshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   } else {
     __syncthreads();
   }
+  mark_phase(ws, 0);
 #pragma unroll 1
   for (size_t f0 = first; f0 < full; f0 += 2 * step) {
     const size_t f1 = f0 + step;
@@ -352,7 +359,7 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
     return full <= lo ? 0 : (full - lo < shard ? full - lo : shard);
   };
   // phase 0: compress the whole local gradient
-  if (CODEC != 0) {
+  if (CODEC != 0 && !c.precompressed) {
     for (int s = 0; s < N; ++s) {
       const size_t base = (size_t)s * shard, lim = shard_full(s);
 #pragma unroll 1
@@ -366,6 +373,7 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   } else {
     __syncthreads();
   }
+  mark_phase(ws, 0);
   // phase 1: reduce my shard from every rank, publish it re-encoded, update my shard's weights
   {
     const size_t base = (size_t)c.rank * shard, lim = shard_full(c.rank);
@@ -400,6 +408,7 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   if (N == 1) return;
   signal_all(c, 1, cta, c.epoch);
   wait_all(c, 1, cta, c.epoch, ws);
+  mark_phase(ws, 1);
   // phase 2: pull every other rank's reduced shard
   for (int dp = 1; dp < N; ++dp) {
     const int p = (c.rank + dp) % N;  // stagger the peers so the links are used evenly
@@ -501,7 +510,7 @@ __device__ void ring_body(const RankCtx& c, int cta, int nctas, WaitStats& ws) {
 template <int ALGO, int CODEC, int MODE>
 __device__ __forceinline__ void run_rank(const RankCtx& c, int cta, int nctas) {
   __shared__ WaitStats ws;
-  if (threadIdx.x == 0) { ws.wait_ns = 0; ws.timeouts = 0; }
+  if (threadIdx.x == 0) { ws.wait_ns = 0; ws.timeouts = 0; ws.mark[0] = 0; ws.mark[1] = 0; }
   const unsigned long long t0 = ptx::globaltimer_ns();
   __syncthreads();
   if (ALGO == AINIC_ALGO_ONESHOT) oneshot_body<CODEC, MODE>(c, cta, nctas, ws);
@@ -516,6 +525,8 @@ __device__ __forceinline__ void run_rank(const RankCtx& c, int cta, int nctas) {
       atomicAdd(c.counters + CTR_WAIT_NS, ws.wait_ns);
       atomicAdd(c.counters + CTR_LAUNCHES, 1ull);
       c.counters[CTR_LAST_NS] = t1 - t0;
+      if (ws.mark[0]) atomicAdd(c.counters + CTR_TO_BARRIER0_NS, ws.mark[0] - t0);
+      if (ws.mark[1]) atomicAdd(c.counters + CTR_TO_BARRIER1_NS, ws.mark[1] - t0);
     }
     __threadfence_system();
     const unsigned long long ticket = atomicAdd(c.counters + CTR_TICKET, 1ull);
@@ -529,10 +540,10 @@ __device__ __forceinline__ void run_rank(const RankCtx& c, int cta, int nctas) {
   }
 }
 
-// Ring: 16 warps (one per frame of a slice).  One-/two-shot: 8-warp CTAs capped at 160 registers,
-// i.e. 40 K registers per CTA, which fits beside a persistent GEMM CTA (192 threads x 80) on one SM.
+// Ring: 16 warps (one per frame of a slice).  One-/two-shot: 8-warp CTAs capped at 144 registers,
+// i.e. 36 K registers per CTA, which fits beside a persistent GEMM CTA (320 threads x 80 = 25.6 K) on one SM.
 #define AINIC_COMM_RING_ATTR __launch_bounds__(kCommThreads)
-#define AINIC_COMM_OVERLAP_ATTR __maxnreg__(160)
+#define AINIC_COMM_OVERLAP_ATTR __maxnreg__(144)
 template <int ALGO>
 constexpr int comm_threads() { return ALGO == AINIC_ALGO_RING ? kCommThreads : kCommThreadsOverlap; }
 

@@ -300,6 +300,20 @@ extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_a
   ctx.epoch = ++c->epoch;
   ctx.parity = (c->parity ^= 1u);
   ctx.timeout_ns = c->timeout_ns;
+  ctx.precompressed = 0;
+  if (a->grad_compressed && a->codec != AINIC_CODEC_F32) {
+    // The GEMM epilogue already produced this rank's frames: read "stage C" from there.  The caller
+    // alternates between two such buffers per bucket, which gives the same reuse guarantee as the
+    // parity halves of the internal staging area.
+    if (!ainic_comm_peer_ptr(c, a->grad_compressed, c->rank)) {
+      set_error("grad_compressed must live in the symmetric heap");
+      return AINIC_ERR_ARG;
+    }
+    for (int p = 0; p < c->nranks; ++p) ctx.stage_c[p] = static_cast<uint8_t*>(ainic_comm_peer_ptr(c, a->grad_compressed, p));
+    ctx.parity = 0;
+    ctx.stage_c_half = 0;
+    ctx.precompressed = 1;
+  }
   return AINIC_OK;
 }
 extern "C" void ainic_set_error_(const char* msg) { set_error(msg ? msg : ""); }

@@ -19,6 +19,7 @@
 #include <string.h>
 
 #if defined(__CUDACC__)
+#include <cuda_fp8.h>
 #define AINIC_HD __host__ __device__ __forceinline__
 #else
 #define AINIC_HD inline
@@ -119,6 +120,11 @@ AINIC_HD float mx_inv_scale(uint32_t sb) { return (sb && sb < 254u) ? u2f((254u 
 
 // fp32 -> e4m3 (bias 7, max 448, no inf, NaN = 0x7F), RNE, saturating.
 AINIC_HD uint32_t f32_to_e4m3(float x) {
+#if defined(__CUDA_ARCH__)
+  // cvt.rn.satfinite.e4m3x2.f32: same rounding (RNE), saturation (448) and NaN code as the
+  // portable path below, which stays the host oracle (tests compare the two bit for bit).
+  return (uint32_t)__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3);
+#else
   uint32_t b = f2u(x);
   uint32_t sign = (b >> 24) & 0x80u;
   uint32_t a = b & 0x7FFFFFFFu;
@@ -137,6 +143,7 @@ AINIC_HD uint32_t f32_to_e4m3(float x) {
   else out = q;                                           // subnormal: q in [0,8], 8 = smallest normal
   if (out > 0x7Eu) out = 0x7Eu;
   return sign | out;
+#endif
 }
 AINIC_HD float e4m3_to_f32(uint32_t v) {
   uint32_t sign = (v & 0x80u) << 24;

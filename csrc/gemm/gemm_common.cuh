@@ -8,6 +8,7 @@
 #include <stdlib.h>
 
 #include "../../include/ainic.h"
+#include "../common/bfp_codec.h"
 #include "../common/ptx.cuh"
 
 namespace ainic {
@@ -18,7 +19,11 @@ using namespace ptx;
 constexpr int BLOCK_M = 128;   // rows per CTA (TMEM has 128 lanes)
 constexpr int BLOCK_K = 64;    // 64 bf16 = 128 B = one swizzle span
 constexpr int UMMA_K = 16;
-constexpr int kThreads = 192;  // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2-5 epilogue
+// warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2-9 epilogue.  Most of the MLP's GEMMs have one tile
+// per CTA, so the epilogue is not hidden behind a next main loop: eight warps (two per TMEM lane
+// quarter, each draining half of the columns) halve that exposed tail.
+constexpr int kThreads = 320;
+constexpr int kEpilogueWarps = 8;
 constexpr int kSmemBudget = 220 * 1024;
 
 struct EpiParams {
@@ -26,11 +31,56 @@ struct EpiParams {
   const float* bias;       // [N] or null (added before activation)
   uint8_t* mask_out;       // [M][ldc] or null: 1 where the (biased) result is > 0 (ReLU mask)
   const uint8_t* mask_in;  // [M][ldc] or null: output zeroed where mask_in == 0 (ReLU backward)
-  float alpha;             // result scale (fp32 output only)
+  float alpha;             // result scale (fp32 / compressed output)
   int relu;                // apply max(0, x)
   int accumulate;          // fp32 output only: c += result
   int M, N, K, ldc;
+  uint8_t* cgrad;          // compressed output (OUT_COMPRESSED): frames of the flat [M][ldc] bucket
+  int codec, bfp_mode;     // AINIC_CODEC_BFP / AINIC_CODEC_MXFP8, AINIC_BFP_*
+  int epi_sleep;           // ns the epilogue warps sleep between polls of the accumulator barrier (0 = spin)
 };
+
+// Output selector of the epilogue.
+constexpr int OUT_BF16 = 0, OUT_FP32 = 1, OUT_COMPRESSED = 2;
+
+// 32 consecutive values of one row -> two BFP16x8 blocks or one MXFP8 block, written straight into
+// the frame layout the all-reduce kernels read (512 mantissa bytes + 32 exponent / 16 scale bytes
+// per 512 values, csrc/common/bfp_codec.h).  This is the reference's BFP adapter sitting directly
+// behind the weight-gradient GEMM: the fp32 gradient never goes to memory and the all-reduce
+// kernel skips its compression pass.  idx = flat index of v[0] (a multiple of 32).
+__device__ __forceinline__ void store_compressed32(const EpiParams& ep, size_t idx, const float (&v)[32]) {
+  const size_t frame = idx >> 9;
+  const uint32_t off = (uint32_t)(idx & 511);
+  if (ep.codec == AINIC_CODEC_BFP) {
+    uint8_t* fr = ep.cgrad + frame * kBfpFrameBytes;
+    uint32_t exps = 0;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      uint32_t E = 0;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) E = max(E, bfp_exp_field(__float_as_uint(v[16 * h + j])));
+      uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+      for (int j = 0; j < 16; ++j) w[j >> 2] |= ((uint32_t)bfp_quant(v[16 * h + j], E, ep.bfp_mode) & 0xFFu) << (8 * (j & 3));
+      *reinterpret_cast<uint4*>(fr + off + 16 * h) = make_uint4(w[0], w[1], w[2], w[3]);
+      exps |= E << (8 * h);
+    }
+    *reinterpret_cast<uint16_t*>(fr + kBfpExpOff + (off >> 4)) = (uint16_t)exps;
+  } else {  // MXFP8
+    uint8_t* fr = ep.cgrad + frame * kMxFrameBytes;
+    uint32_t E = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) E = max(E, bfp_exp_field(__float_as_uint(v[j])));
+    const uint32_t sb = mx_scale_byte(E);
+    const float inv = mx_inv_scale(sb);
+    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int j = 0; j < 32; ++j) w[j >> 2] |= f32_to_e4m3(v[j] * inv) << (8 * (j & 3));
+    *reinterpret_cast<uint4*>(fr + off) = make_uint4(w[0], w[1], w[2], w[3]);
+    *reinterpret_cast<uint4*>(fr + off + 16) = make_uint4(w[4], w[5], w[6], w[7]);
+    fr[kMxScaleOff + (off >> 5)] = (uint8_t)sb;
+  }
+}
 
 // Shared-memory matrix descriptor (sm_100 format, version 1, SWIZZLE_128B).
 //   K-major operand : rows of 128 B, 8-row core-matrix groups SBO = 1024 B apart (LBO unused).
@@ -65,11 +115,17 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 
 // Drain one 128 x BLOCK_N accumulator: thread `lane` of the warp owning TMEM lane quarter q reads
 // row (32 q + lane) 32 columns at a time and writes it with the fused epilogue.
-template <int BLOCK_N, bool OUT_F32>
-__device__ __forceinline__ void epilogue_store(const EpiParams& ep, uint32_t taddr, int row, int n0) {
+template <int BLOCK_N, int OUT>
+__device__ __forceinline__ void epilogue_store(const EpiParams& ep, uint32_t taddr, int row, int n0, int half, int nsplit) {
+  constexpr bool OUT_F32 = OUT == OUT_FP32;
+  static_assert(OUT != OUT_COMPRESSED || BLOCK_N % 32 == 0, "compressed output works on whole 32-column chunks");
   const bool row_ok = row < ep.M;
+  // with 8 epilogue warps two of them share each TMEM lane quarter: `half` 0 drains the first half of the
+  // column chunks, `half` 1 the rest; with 4 warps (nsplit == 1) each drains all of them
+  constexpr int kChunks = BLOCK_N / 32 + (BLOCK_N % 32 ? 1 : 0);
+  const int c_begin = (nsplit == 2 && half) ? kChunks / 2 : 0, c_end = (nsplit == 2 && !half) ? kChunks / 2 : kChunks;
 #pragma unroll 1
-  for (int c = 0; c < BLOCK_N / 32 + (BLOCK_N % 32 ? 1 : 0); ++c) {
+  for (int c = c_begin; c < c_end; ++c) {
     uint32_t r[32];
     if (BLOCK_N % 32 == 0 || c < BLOCK_N / 32) {
       tmem_ld_32x32b_x32(taddr + c * 32, r);
@@ -82,6 +138,15 @@ __device__ __forceinline__ void epilogue_store(const EpiParams& ep, uint32_t tad
     tmem_ld_wait();
     const int ncols = (BLOCK_N % 32 == 0 || c < BLOCK_N / 32) ? 32 : 16;
     const int col0 = n0 + c * 32;
+    if constexpr (OUT == OUT_COMPRESSED) {
+      if (row_ok && col0 < ep.N) {   // host guarantees N % 32 == 0 and ldc % 32 == 0
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * ep.alpha;
+        store_compressed32(ep, (size_t)row * ep.ldc + col0, v);
+      }
+      continue;
+    }
     if (row_ok && col0 < ep.N) {
       const size_t off = (size_t)row * ep.ldc + col0;
 #pragma unroll
@@ -214,6 +279,18 @@ inline int num_sms() {
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
   }
   return n;
+}
+
+// Threads per CTA: 2 non-epilogue warps + 4 (default) or 8 (AINIC_GEMM_EPI_WARPS=8) epilogue warps.
+// Measured on the reference shape: 8 warps do not shorten the exposed epilogue enough to pay for the
+// extra polling warps (0.626 vs 0.620 ms/step at 1 GPU, 0.815 vs 0.768 at 2), so 4 is the default.
+inline int gemm_threads() {
+  static const int t = (getenv("AINIC_GEMM_EPI_WARPS") && atoi(getenv("AINIC_GEMM_EPI_WARPS")) == 8) ? kThreads : 192;
+  return t;
+}
+inline int gemm_epi_sleep_ns() {
+  static const int v = getenv("AINIC_GEMM_EPI_SLEEP") ? atoi(getenv("AINIC_GEMM_EPI_SLEEP")) : 0;
+  return v;
 }
 
 inline bool pdl_enabled() {

@@ -30,7 +30,7 @@ __host__ __device__ constexpr uint32_t tmem_cols(int block_n) {
   return 2 * block_n <= 32 ? 32u : 2 * block_n <= 64 ? 64u : 2 * block_n <= 128 ? 128u : 2 * block_n <= 256 ? 256u : 512u;
 }
 
-template <int BLOCK_N, bool A_MN, bool B_MN, bool OUT_F32>
+template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, EpiParams ep) {
   constexpr int kStages = num_stages(BLOCK_N);
@@ -53,6 +53,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int epi_warps = (int)(blockDim.x >> 5) - 2;   // 4 or 8 (two per TMEM lane quarter)
 
   const int m_tiles = (ep.M + BLOCK_M - 1) / BLOCK_M;
   const int n_tiles = (ep.N + BLOCK_N - 1) / BLOCK_N;
@@ -68,7 +69,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);
-      mbar_init(&tmem_empty[s], 4);
+      mbar_init(&tmem_empty[s], epi_warps);
     }
     fence_barrier_init();
   }
@@ -148,10 +149,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m0 = (tile % m_tiles) * BLOCK_M;
       const int n0 = (tile / m_tiles) * BLOCK_N;
-      mbar_wait(&tmem_full[acc], acc_phase);
+      mbar_wait_backoff(&tmem_full[acc], acc_phase, (uint32_t)ep.epi_sleep);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N);
-      epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0);
+      epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
@@ -168,7 +169,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   }
 }
 
-template <int BLOCK_N, bool A_MN, bool B_MN, bool OUT_F32>
+template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
 static int launch(const void* a, int lda, const void* b, int ldb, const EpiParams& ep, int max_ctas,
                   cudaStream_t stream) {
   CUtensorMap ta, tb;
@@ -193,7 +194,7 @@ static int launch(const void* a, int lda, const void* b, int ldb, const EpiParam
   if (tiles < grid) grid = tiles;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kThreads);
+  cfg.blockDim = dim3(gemm_threads());
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -233,6 +234,7 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
   ep.c = c;
   ep.M = M; ep.N = N; ep.K = K; ep.ldc = ldc;
   ep.alpha = 1.0f;
+  ep.epi_sleep = gemm_epi_sleep_ns();
   if (epi) {
     ep.bias = epi->bias;
     ep.mask_out = epi->mask_out;
@@ -240,6 +242,15 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
     ep.relu = epi->relu;
     ep.accumulate = epi->accumulate;
     ep.alpha = epi->alpha;
+    ep.cgrad = static_cast<uint8_t*>(epi->cgrad);
+    ep.codec = epi->codec;
+    ep.bfp_mode = epi->bfp_mode;
+  }
+  if (ep.cgrad) {  // compressed gradient output: backward-weight layout only, whole 32-value groups
+    if (layout != AINIC_GEMM_TN || (N % 32) || (ldc % 32) || ((uintptr_t)ep.cgrad & 15) ||
+        (ep.codec != AINIC_CODEC_BFP && ep.codec != AINIC_CODEC_MXFP8))
+      return AINIC_ERR_ARG;
+    if (block_n < 0) return AINIC_ERR_UNSUPPORTED;
   }
   const int sms = (max_ctas > 0 && max_ctas < num_sms()) ? max_ctas : num_sms();
   if (block_n == 0) {
@@ -279,7 +290,15 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
         DISPATCH_BN(128, false, true, false)
         default: return AINIC_ERR_ARG;
       }
-    case AINIC_GEMM_TN:  // C = A[K,M]^T . B[K,N], fp32 out
+    case AINIC_GEMM_TN:  // C = A[K,M]^T . B[K,N], fp32 out (or compressed frames)
+      if (ep.cgrad) {
+        switch (block_n) {
+          DISPATCH_BN(256, true, true, OUT_COMPRESSED)
+          DISPATCH_BN(192, true, true, OUT_COMPRESSED)
+          DISPATCH_BN(128, true, true, OUT_COMPRESSED)
+          default: return AINIC_ERR_ARG;
+        }
+      }
       switch (block_n) {
         DISPATCH_BN(256, true, true, true)
         DISPATCH_BN(192, true, true, true)

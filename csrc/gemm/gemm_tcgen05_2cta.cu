@@ -23,7 +23,7 @@ __host__ __device__ constexpr int num_stages2(int block_n) {
 }
 __host__ __device__ constexpr uint32_t tmem_cols2(int block_n) { return 2 * block_n <= 128 ? 128u : 2 * block_n <= 256 ? 256u : 512u; }
 
-template <int BLOCK_N, bool A_MN, bool B_MN, bool OUT_F32>
+template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, EpiParams ep) {
   constexpr int HALF_N = BLOCK_N / 2;
@@ -47,6 +47,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int epi_warps = (int)(blockDim.x >> 5) - 2;   // 4 or 8 (two per TMEM lane quarter)
   const uint32_t cta_rank = cluster_ctarank();   // 0 = leader (issues the MMAs), 1 = peer
   const bool leader = cta_rank == 0;
   const int cluster_id = blockIdx.x >> 1;
@@ -66,7 +67,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full[s], 1);   // multicast tcgen05.commit
-      mbar_init(&tmem_empty[s], 8);  // leader: 4 epilogue warps of each CTA
+      mbar_init(&tmem_empty[s], 2 * epi_warps);  // leader: the epilogue warps of both CTAs
     }
     fence_barrier_init();
   }
@@ -149,10 +150,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       const int m0 = (tile % m_tiles) * (2 * BLOCK_M) + (int)cta_rank * BLOCK_M;
       const int n0 = (tile / m_tiles) * BLOCK_N;
-      mbar_wait(&tmem_full[acc], acc_phase);
+      mbar_wait_backoff(&tmem_full[acc], acc_phase, (uint32_t)ep.epi_sleep);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N);
-      epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0);
+      epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
@@ -172,7 +173,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   }
 }
 
-template <int BLOCK_N, bool A_MN, bool B_MN, bool OUT_F32>
+template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
 static int launch2(const void* a, int lda, const void* b, int ldb, const EpiParams& ep, int max_ctas, cudaStream_t stream) {
   constexpr int HALF_N = BLOCK_N / 2;
   CUtensorMap ta, tb;
@@ -198,7 +199,7 @@ static int launch2(const void* a, int lda, const void* b, int ldb, const EpiPara
   if (tiles < clusters) clusters = tiles;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(2 * clusters);
-  cfg.blockDim = dim3(kThreads);
+  cfg.blockDim = dim3(gemm_threads());
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];

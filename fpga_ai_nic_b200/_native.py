@@ -30,12 +30,13 @@ ERRORS = {0: "ok", -1: "bad argument", -2: "CUDA error", -3: "timeout", -4: "bus
 
 class GemmEpilogue(C.Structure):
     _fields_ = [("bias", vp), ("mask_out", vp), ("mask_in", vp), ("alpha", C.c_float), ("relu", C.c_int),
-                ("accumulate", C.c_int)]
+                ("accumulate", C.c_int), ("cgrad", vp), ("codec", C.c_int), ("bfp_mode", C.c_int)]
 
 
 class AllreduceArgs(C.Structure):
     _fields_ = [("grad", vp), ("weight", vp), ("weight_bf16", vp), ("grad_out", vp), ("count", sz), ("lr", C.c_float),
-                ("codec", C.c_int), ("bfp_mode", C.c_int), ("algo", C.c_int), ("max_ctas", C.c_int)]
+                ("codec", C.c_int), ("bfp_mode", C.c_int), ("algo", C.c_int), ("max_ctas", C.c_int),
+                ("grad_compressed", vp)]
 
 
 class Rqst(C.Structure):

@@ -52,7 +52,9 @@ class MLPConfig:
         p = self.param_count()
         biggest = max(self.sizes[l] * self.sizes[l + 1] for l in range(self.nlayers))
         frames = (biggest + 511) // 512
-        return p * 8 + frames * (2 * 1024 + 2 * 2048) + (8 << 20) + self.nlayers * 16384
+        # fp32 weights + fp32 gradients, two compressed-gradient buffers per layer (GEMM epilogue output),
+        # the communicator's staging for the largest bucket, slack for alignment
+        return p * 8 + p * 3 + frames * (2 * 1024 + 2 * 2048) + (8 << 20) + self.nlayers * 32768
 
 
 class MLPTrainer:

@@ -146,13 +146,27 @@ def gemm_bwd_data(dy: torch.Tensor, w: torch.Tensor, mask_in: torch.Tensor | Non
 
 
 def gemm_bwd_weight(dy: torch.Tensor, x: torch.Tensor, out: torch.Tensor | None = None, accumulate: bool = False,
-                    alpha: float = 1.0, block_n: int = 0, max_ctas: int = 0, stream=None) -> torch.Tensor:
-    """dw[n,k] = dy[mb,n]^T @ x[mb,k] as fp32, written straight into the flat gradient bucket."""
+                    alpha: float = 1.0, block_n: int = 0, max_ctas: int = 0, stream=None,
+                    compressed_out: torch.Tensor | None = None, codec: int = CODEC_BFP, bfp_mode: int = CLEAN) -> torch.Tensor:
+    """dw[n,k] = dy[mb,n]^T @ x[mb,k] as fp32, written straight into the flat gradient bucket.
+
+    With ``compressed_out`` (uint8, ``bfp_bytes(n*k)`` / ``mx_bytes(n*k)``) the epilogue instead emits the
+    gradient already in BFP / MXFP8 frame layout - what ``Communicator.allreduce_fused(grad_compressed=...)``
+    consumes - and no fp32 gradient is written."""
     _chk(dy, torch.bfloat16)
     _chk(x, torch.bfloat16)
     mb, n = dy.shape
     k = x.shape[1]
     assert x.shape[0] == mb
+    if compressed_out is not None:
+        _chk(compressed_out, torch.uint8)
+        epi = N.GemmEpilogue(None, None, None, alpha, 0, 0, compressed_out.data_ptr(), codec, bfp_mode)
+        lib = N.cuda()
+        rc = lib.ainic_gemm_bf16(GEMM_TN, dy.data_ptr(), dy.stride(0), x.data_ptr(), x.stride(0), None, k, n, k, mb,
+                                 C.byref(epi), block_n, max_ctas, N.stream_ptr(stream))
+        N.check(rc, "gemm_bf16(compressed)")
+        _count()
+        return compressed_out
     if out is None:
         out = torch.empty(n, k, dtype=torch.float32, device=dy.device)
     epi = N.GemmEpilogue(None, None, None, alpha, 0, int(accumulate))

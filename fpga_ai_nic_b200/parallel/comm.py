@@ -82,11 +82,11 @@ class Communicator:
     def allreduce_fused(self, grad: torch.Tensor, weight: torch.Tensor | None = None, lr: float = 0.0,
                         weight_bf16: torch.Tensor | None = None, grad_out: torch.Tensor | None = None,
                         codec: int = K.CODEC_BFP, bfp_mode: int = K.CLEAN, algo: int = K.ALGO_AUTO, max_ctas: int = 0,
-                        stream=None) -> None:
+                        stream=None, grad_compressed: torch.Tensor | None = None) -> None:
         a = N.AllreduceArgs(grad.data_ptr(), weight.data_ptr() if weight is not None else None,
                             weight_bf16.data_ptr() if weight_bf16 is not None else None,
                             grad_out.data_ptr() if grad_out is not None else None, grad.numel(), lr, codec, bfp_mode,
-                            algo, max_ctas)
+                            algo, max_ctas, grad_compressed.data_ptr() if grad_compressed is not None else None)
         N.check(self.lib.ainic_allreduce_fused(self.handle, C.byref(a), N.stream_ptr(stream)), "allreduce_fused")
         K._count()
 
@@ -152,7 +152,8 @@ class Communicator:
     def counters(self) -> dict:
         out = (C.c_uint64 * 8)()
         N.check(self.lib.ainic_comm_counters(self.handle, out), "comm_counters")
-        return {"busy_ns": out[0], "wait_ns": out[1], "launches": out[2], "timeouts": out[3], "last_ns": out[5]}
+        return {"busy_ns": out[0], "wait_ns": out[1], "launches": out[2], "timeouts": out[3], "last_ns": out[5],
+                "to_barrier0_ns": out[6], "to_barrier1_ns": out[7]}
 
     def close(self) -> None:
         if not self._closed:

@@ -69,6 +69,11 @@ typedef struct ainic_gemm_epilogue {
   float alpha;            /* fp32 outputs: scale */
   int relu;
   int accumulate;         /* fp32 outputs: C += result */
+  void* cgrad;            /* AINIC_GEMM_TN only, nullable: write the result as BFP/MXFP8 frames of the flat
+                             [M][ldc] bucket instead of fp32 (the layout ainic_allreduce_fused reads when
+                             args.grad_compressed is set); needs N % 32 == 0 and ldc % 32 == 0 */
+  int codec;              /* AINIC_CODEC_BFP or AINIC_CODEC_MXFP8 when cgrad is set */
+  int bfp_mode;
 } ainic_gemm_epilogue_t;
 /* bf16 operands, fp32 accumulation on tcgen05 tensor cores.  block_n = 0 picks the tile width,
  * max_ctas = 0 uses every SM (a smaller value leaves SMs for a concurrent all-reduce kernel). */
@@ -110,6 +115,10 @@ typedef struct ainic_allreduce_args {
   float lr;
   int codec, bfp_mode, algo;
   int max_ctas;       /* 0 = default */
+  void* grad_compressed; /* nullable: this rank's gradient already in `codec` frame layout inside the symmetric
+                            heap (written by the GEMM epilogue); the kernel then skips its compression pass and
+                            `grad` is only used for its size.  The caller alternates between two such buffers
+                            from call to call on the same bucket. */
 } ainic_allreduce_args_t;
 /* Fused compress -> (peer pull) -> fp32 reduce -> decompress -> SGD, one kernel launch on stream. */
 int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args_t* args, void* stream);

@@ -90,6 +90,38 @@ for count in (8192 * 5 + 777, 1 << 20):
         if world > 1:
             dist.barrier()
 
+# ------------------------------------------------------------------ 1a. gradient pre-compressed by the producer
+# (what the weight-gradient GEMM epilogue does in the trainer): the kernel skips its own compression
+count = 1 << 20
+cbufs = [comm.empty(K.bfp_bytes(count), dtype=torch.uint8) for _ in range(2)]
+for it, (algo, codec, mode) in enumerate([("oneshot", "bfp", O.CLEAN), ("twoshot", "bfp", O.CLEAN), ("twoshot", "mxfp8", 0),
+                                          ("oneshot", "bfp", O.HW_EXACT)]):
+    gen = torch.Generator().manual_seed(900 + 10 * it + rank)
+    g = torch.randn(count, generator=gen) * 1e-3
+    w0 = torch.randn(count, generator=torch.Generator().manual_seed(9))
+    gv, wv = g_heap[:count], w_heap[:count]
+    gv.copy_(g)
+    wv.copy_(w0)
+    cb = cbufs[it & 1]
+    if codec == "bfp":
+        K.bfp_compress(gv, mode, out=cb)
+    else:
+        K.mx_compress(gv, out=cb[:K.mx_bytes(count)])
+    all_g = gather(gv)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    comm.allreduce_fused(gv, wv, 0.1, sh[:count], codec=K.CODEC_NAMES[codec], bfp_mode=mode, algo=K.ALGO_NAMES[algo],
+                         grad_compressed=cb)
+    torch.cuda.synchronize()
+    want = O.allreduce(all_g, algo, K.CODEC_NAMES[codec], mode)
+    ok = all_ok(torch.equal(wv.cpu(), O.sgd(w0, want[rank], 0.1)))
+    say(check="allreduce_precompressed", algo=algo, codec=codec, mode=mode, world=world, ok=ok, timeouts=comm.counters()["timeouts"])
+    if not ok:
+        fails.append(("precompressed", algo, codec))
+    if world > 1:
+        dist.barrier()
+
 # ------------------------------------------------------------------ 1b. NVLS (multimem) all-reduce + SGD
 if world > 1:
     have = comm.enable_nvls(64 << 20)
