@@ -73,7 +73,10 @@ def main():
     for codec in ([c["codec"], "f32"] if world > 1 else ["f32"]):
         cfg = MLPConfig.reference(c["layers"], c["width"], c["mb"])
         cfg.codec = codec
-        cfg.lr = 0.5
+        cfg.lr = 0.05
+        # the reference's init (std 0.029) makes activations grow ~sqrt(width)*0.029 per layer; rescale to
+        # variance-preserving so that 16 layers of width 16384 stay finite in bf16
+        cfg.init_scale = (1.0 / c["width"] ** 0.5) / 0.0289
         tr = MLPTrainer(cfg)
         ms = timed(tr, x, y, a.steps, a.warmup, world)
         res[f"ms_per_step_{codec}"] = ms

@@ -85,11 +85,17 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
   // With more than one rank and a block-compressed wire format the weight-gradient GEMM writes the
   // wire format itself (the reference's BFP adapter sits right behind the adder tree the same way,
   // hw/all_reduce.sv:745-772): no fp32 gradient in memory, no compression pass in the all-reduce.
-  // Opt-in (AINIC_FUSE_COMPRESS=1): it takes ~10 us off every all-reduce call but the quantisation
-  // lengthens the GEMM's exposed epilogue, which at 2 ranks costs more than it saves (0.80 vs 0.77
-  // ms/step); it pays when the all-reduce queue, not the GEMM chain, is the critical path.
-  m->fuse_compress = ainic_comm_size(comm) > 1 && (codec == AINIC_CODEC_BFP || codec == AINIC_CODEC_MXFP8) &&
-                     getenv("AINIC_FUSE_COMPRESS") && atoi(getenv("AINIC_FUSE_COMPRESS")) == 1;
+  // It takes 10-20 us off every all-reduce call but the quantisation lengthens the GEMM's exposed
+  // epilogue.  Measured on the reference MLP: at 2 ranks it costs more than it saves (0.80 vs 0.77
+  // ms/step), at 8 ranks - where the all-reduce queue, not the GEMM chain, is the critical path - it
+  // wins (1.04 vs 1.16 ms/step); 4 ranks are a wash (0.95 vs 0.94).  Default: on from 8 ranks;
+  // AINIC_FUSE_COMPRESS=0/1 overrides.
+  {
+    const int n = ainic_comm_size(comm);
+    bool on = n >= 8;
+    if (const char* e = getenv("AINIC_FUSE_COMPRESS")) on = atoi(e) == 1;
+    m->fuse_compress = on && n > 1 && (codec == AINIC_CODEC_BFP || codec == AINIC_CODEC_MXFP8);
+  }
   m->layers.resize(nlayers);
   m->act.resize(nlayers + 1);
   m->dact.resize(nlayers + 1);

@@ -392,14 +392,8 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
         // publish, then apply exactly what the peers will decode (fixes SURVEY D11)
         uint8_t* d0 = c.stage_d[c.rank] + j0 * FC::kBytes;
         uint8_t* d1 = c.stage_d[c.rank] + j1 * FC::kBytes;
-        FC::encode(acc0, d0, lane);
-        if (has1) FC::encode(acc1, d1, lane);
-        __syncwarp();
-        typename FC::Raw r0, r1;
-        FC::load(d0, r0, lane);
-        if (has1) FC::load(d1, r1, lane);
-        FC::unpack(r0, acc0, lane);
-        if (has1) FC::unpack(r1, acc1, lane);
+        frame_encode_rt<CODEC, MODE>(acc0, d0, lane);
+        if (has1) frame_encode_rt<CODEC, MODE>(acc1, d1, lane);
       }
       apply_pair(c, f0, f1, has1, acc0, acc1, lane);
     }

@@ -86,6 +86,29 @@ struct FrameCodec<1, MODE> {
     }
     frame[kBfpExpOff + lane] = (uint8_t)e_lane;
   }
+  // encode + replace v by what a reader of the frame will decode (no trip through memory)
+  __device__ static __forceinline__ void encode_rt(float (&v)[16], uint8_t* frame, int lane) {
+    uint32_t e_lane = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t E = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) E = max(E, bfp_exp_field(__float_as_uint(v[4 * i + j])));
+      E = max(E, __shfl_xor_sync(kFullMask, E, 1));
+      E = max(E, __shfl_xor_sync(kFullMask, E, 2));
+      uint32_t word = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int32_t q = bfp_quant(v[4 * i + j], E, MODE);
+        word |= ((uint32_t)q & 0xFFu) << (8 * j);
+        v[4 * i + j] = bfp_dequant((int32_t)(int8_t)q, E, MODE);
+      }
+      *reinterpret_cast<uint32_t*>(frame + i * 128 + lane * 4) = word;
+      const uint32_t t = __shfl_sync(kFullMask, E, (lane & 7) * 4);
+      if ((lane >> 3) == i) e_lane = t;
+    }
+    frame[kBfpExpOff + lane] = (uint8_t)e_lane;
+  }
 };
 
 // ---------------------------------------------------------------- MXFP8 (e4m3 + ue8m0 / 32)
@@ -167,6 +190,19 @@ __device__ __forceinline__ void frame_decode(const uint8_t* frame, float (&v)[16
   typename FrameCodec<CODEC, MODE>::Raw r;
   FrameCodec<CODEC, MODE>::load(frame, r, lane);
   FrameCodec<CODEC, MODE>::unpack(r, v, lane);
+}
+
+// Encode v into `frame` and leave in v exactly what a reader of the frame will decode.  BFP does it
+// in registers; the other codecs read their own bytes back (L2 hit).
+template <int CODEC, int MODE>
+__device__ __forceinline__ void frame_encode_rt(float (&v)[16], uint8_t* frame, int lane) {
+  if constexpr (CODEC == 1) {
+    FrameCodec<1, MODE>::encode_rt(v, frame, lane);
+  } else {
+    FrameCodec<CODEC, MODE>::encode(v, frame, lane);
+    __syncwarp();
+    frame_decode<CODEC, MODE>(frame, v, lane);
+  }
 }
 
 // ---------------------------------------------------------------- fp32 frame load / store with tail predication

@@ -29,6 +29,7 @@ class MLPConfig:
     bfp_mode: int = K.CLEAN
     algo: str = "auto"
     seed: int = 1                                              # libxsmm_rng_set_seed(1), :273
+    init_scale: float = 1.0                                    # multiplies the reference init (wide layers need < 1)
 
     @staticmethod
     def reference(nlayers: int = 10, width: int = 2048, mb: int = 1792) -> "MLPConfig":
@@ -107,7 +108,7 @@ class MLPTrainer:
         uses the same seed, which is what rank 0's MPI_Bcast achieves in the reference (:463-470)."""
         for l in range(self.cfg.nlayers):
             w = self.buffer("weight", l)
-            w.copy_(O.init_buf(w.numel(), seed=self.cfg.seed * 1000 + l).view_as(w))
+            w.copy_(O.init_buf(w.numel(), seed=self.cfg.seed * 1000 + l).view_as(w) * self.cfg.init_scale)
             self.buffer("bias", l).copy_(O.init_buf(self.cfg.sizes[l + 1], seed=self.cfg.seed * 1000 + 500 + l))
         self.sync_shadows()
 
