@@ -51,6 +51,12 @@ struct ainic_mlp {
   float* loss_sum = nullptr;         // device scalar
   cudaStream_t wgrad_stream = nullptr, comm_stream = nullptr;
   cudaEvent_t fwd_done = nullptr;
+  // DETAILED_PROFILE of the reference (sw/mlp_mpi_example_f32.cpp:32, :699-751): timestamps on the
+  // main stream at step start / forward end / loss end / backward end, plus the last update.
+  bool profile = false;
+  cudaEvent_t prof[5] = {};
+  double phase_ms[4] = {0, 0, 0, 0};   // fwd_fc, loss (fwd+bwd), bwdupd_fc, update tail; accumulated
+  unsigned long long prof_steps = 0;
   bool first_step = true;
   unsigned long long launches = 0;
   unsigned long long step_idx = 0;
@@ -223,12 +229,19 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
   if (!m->first_step) TRY_CUDA(cudaStreamWaitEvent(s, m->layers[0].dw_ready, 0));
   if (x_bf16 != m->act[0])
     TRY_CUDA(cudaMemcpyAsync(m->act[0], x_bf16, (size_t)m->mb * m->layers[0].in * 2, cudaMemcpyDeviceToDevice, s));
+  if (m->profile) TRY_CUDA(cudaEventRecord(m->prof[0], s));
   TRY(forward(m, s, true));
+  if (m->profile) TRY_CUDA(cudaEventRecord(m->prof[1], s));
   TRY_CUDA(cudaMemsetAsync(m->loss_sum, 0, 4, s));
   TRY(ainic_softmax_xent(m->act[Ln], labels, nullptr, m->dact[Ln], m->loss_sum, m->mb, m->layers[Ln - 1].out,
                          m->layers[Ln - 1].out, m->loss_weight, s));
   m->launches++;
   if (loss_out) TRY_CUDA(cudaMemcpyAsync(loss_out, m->loss_sum, 4, cudaMemcpyDeviceToDevice, s));
+  if (relu) {  // the last layer's ReLU sits between the logits and the loss
+    TRY(ainic_apply_mask_bf16(m->dact[Ln], m->layers[Ln - 1].mask, (size_t)m->mb * m->layers[Ln - 1].out, s));
+    m->launches++;
+  }
+  if (m->profile) TRY_CUDA(cudaEventRecord(m->prof[2], s));
   for (int l = Ln - 1; l >= 0; --l) {
     Layer& L = m->layers[l];
     // dact[l+1] is final here (for ReLU layers the mask was already applied by the producer below)
@@ -281,7 +294,36 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
   }
   m->first_step = false;
   m->step_idx++;
+  if (m->profile) {
+    // profiling mode serialises the step: backward end on the main stream, then the last update
+    TRY_CUDA(cudaEventRecord(m->prof[3], s));
+    for (auto& L : m->layers) TRY_CUDA(cudaStreamWaitEvent(s, L.updated, 0));
+    TRY_CUDA(cudaEventRecord(m->prof[4], s));
+    TRY_CUDA(cudaEventSynchronize(m->prof[4]));
+    for (int i = 0; i < 4; ++i) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, m->prof[i], m->prof[i + 1]);
+      m->phase_ms[i] += ms;
+    }
+    m->prof_steps++;
+  }
   return AINIC_OK;
+}
+
+// Per-phase device times accumulated since profiling was switched on (ms): [0] forward FC,
+// [1] loss fwd+bwd, [2] backward + weight-gradient FC, [3] tail until the last weight update landed;
+// returns the number of profiled steps.  enable != 0 switches the mode on (and clears), 0 off.
+extern "C" unsigned long long ainic_mlp_profile(ainic_mlp_t* m, int enable, double out_ms[4]) {
+  if (!m) return 0;
+  const unsigned long long n = m->prof_steps;
+  if (out_ms) for (int i = 0; i < 4; ++i) out_ms[i] = m->phase_ms[i];
+  if (enable >= 0) {
+    if (enable && !m->prof[0])
+      for (auto& e : m->prof) cudaEventCreate(&e);
+    m->profile = enable != 0;
+    if (enable) { for (auto& p : m->phase_ms) p = 0; m->prof_steps = 0; }
+  }
+  return n;
 }
 
 // Block the given stream until every outstanding weight update has landed (the reference's

@@ -114,9 +114,34 @@ __global__ void __launch_bounds__(256) bias_grad_kernel(const __nv_bfloat16* __r
   }
 }
 
+// x[i] = mask[i] ? x[i] : 0  (ReLU backward on the loss gradient when the last layer has a ReLU)
+__global__ void __launch_bounds__(256) apply_mask_kernel(__nv_bfloat16* __restrict__ x, const uint8_t* __restrict__ mask, size_t count) {
+  const size_t n8 = count >> 3;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    uint4 v = reinterpret_cast<uint4*>(x)[i];
+    const uint2 m = reinterpret_cast<const uint2*>(mask)[i];
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const uint32_t mb = ((j < 4 ? m.x : m.y) >> (8 * (j & 3))) & 0xFFu;
+      if (!mb) w[j >> 1] &= (j & 1) ? 0x0000FFFFu : 0xFFFF0000u;
+    }
+    reinterpret_cast<uint4*>(x)[i] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
 }  // namespace ainic
 
 using namespace ainic;
+
+extern "C" int ainic_apply_mask_bf16(void* x, const uint8_t* mask, size_t count, void* stream) {
+  if (!x || !mask || count == 0 || (count % 8) || ((uintptr_t)x & 15) || ((uintptr_t)mask & 7)) return AINIC_ERR_ARG;
+  size_t blocks = (count / 8 + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  apply_mask_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)x, mask, count);
+  return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
+}
 
 extern "C" int ainic_softmax_xent(const void* logits, const int32_t* labels, void* probs, void* dlogits,
                                   float* loss_sum, int mb, int n, int ld, float loss_weight, void* stream) {

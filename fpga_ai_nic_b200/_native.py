@@ -161,6 +161,8 @@ def cuda() -> C.CDLL:
     lib.ainic_mlp_forward.argtypes = [vp, vp, vp]
     lib.ainic_mlp_step.argtypes = [vp, vp, vp, vp, vp]
     lib.ainic_mlp_wait_updates.argtypes = [vp, vp]
+    lib.ainic_mlp_profile.restype = C.c_ulonglong
+    lib.ainic_mlp_profile.argtypes = [vp, C.c_int, C.POINTER(C.c_double)]
     lib.ainic_mlp_launches.restype = C.c_ulonglong
     lib.ainic_mlp_launches.argtypes = [vp]
     lib.ainic_mlp_loss_ptr.restype = vp

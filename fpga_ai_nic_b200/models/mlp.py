@@ -135,6 +135,23 @@ class MLPTrainer:
         """Make the current stream wait for all outstanding weight updates (reference: wait(), :157-180)."""
         N.check(self.lib.ainic_mlp_wait_updates(self.handle, N.stream_ptr()), "mlp_wait_updates")
 
+    # -- profiling / health ------------------------------------------------------------------------
+    def profile(self, enable: bool | None = None) -> dict:
+        """Per-phase device times (the reference's DETAILED_PROFILE).  ``profile(True)`` starts, ``profile(False)``
+        stops, ``profile()`` reads: {'steps', 'fwd_fc', 'loss', 'bwdupd_fc', 'update_tail'} in ms (accumulated)."""
+        out = (C.c_double * 4)()
+        n = self.lib.ainic_mlp_profile(self.handle, -1 if enable is None else int(enable), out)
+        return {"steps": int(n), "fwd_fc": out[0], "loss": out[1], "bwdupd_fc": out[2], "update_tail": out[3]}
+
+    def check_health(self) -> dict:
+        """Failure detection: raises if any fused all-reduce gave up waiting for a peer (the reference's
+        wait() would spin forever).  Returns the communicator's counters otherwise."""
+        ctr = self.comm.counters()
+        if ctr["timeouts"]:
+            raise N.NativeError(f"{ctr['timeouts']} flag waits timed out inside fused all-reduce kernels: a peer rank is "
+                                "stuck or dead; weights on this rank are no longer trustworthy")
+        return ctr
+
     @property
     def launches(self) -> int:
         return int(self.lib.ainic_mlp_launches(self.handle))

@@ -84,6 +84,8 @@ int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b, int ldb, 
  * (libxsmm_dnn_smax_{fwd,bwd}_exec_f32, sw/mlp_mpi_example_f32.cpp:718-728) */
 int ainic_softmax_xent(const void* logits_bf16, const int32_t* labels, void* probs_bf16 /*nullable*/,
                        void* dlogits_bf16, float* loss_sum, int mb, int n, int ld, float loss_weight, void* stream);
+/* x[i] = mask[i] ? x[i] : 0 on bf16 data (ReLU backward of the loss gradient); count % 8 == 0 */
+int ainic_apply_mask_bf16(void* x_bf16, const uint8_t* mask, size_t count, void* stream);
 /* dbias[n] = sum over rows of dy[mb][n] (bf16 in, fp32 out) */
 int ainic_bias_grad(const void* dy_bf16, float* dbias, int mb, int n, int ld, void* stream);
 
@@ -183,6 +185,10 @@ int ainic_mlp_forward(ainic_mlp_t* m, const void* x_bf16, void* stream);
 int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t* labels, float* loss_out /*device, nullable*/,
                    void* stream);
 int ainic_mlp_wait_updates(ainic_mlp_t* m, void* stream);
+/* DETAILED_PROFILE (sw/mlp_mpi_example_f32.cpp:32, :809-815): enable = 1 starts (and clears) per-phase device
+ * timing, 0 stops it, -1 only reads.  out_ms: forward FC, loss, backward+weight-gradient FC, tail until the
+ * last weight update; returns the number of profiled steps.  Profiling serialises the step at its end. */
+unsigned long long ainic_mlp_profile(ainic_mlp_t* m, int enable, double out_ms[4]);
 unsigned long long ainic_mlp_launches(ainic_mlp_t* m);
 void* ainic_mlp_loss_ptr(ainic_mlp_t* m);
 

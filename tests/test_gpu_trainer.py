@@ -1,0 +1,127 @@
+"""The native MLP trainer on one GPU: every fuse mode against the CPU oracle of
+sw/mlp_mpi_example_f32.cpp's math, checkpoint / resume, per-phase profile,
+health check and the reference-compatible command line."""
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from fpga_ai_nic_b200.ops import oracle as O
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _oracle_steps(cfg, w_init, b, x, y, steps):
+    """fp32 oracle with the same bf16 roundings the GPU path applies to activations / weights."""
+    W = [w.clone() for w in w_init]
+    bf = lambda t: t.bfloat16().float()
+    losses = []
+    for _ in range(steps):
+        acts, masks = [bf(x)], []
+        for l in range(cfg.nlayers):
+            yl, m = O.fc_fwd(acts[-1], bf(W[l]), b[l], cfg.fuse)
+            acts.append(bf(yl))
+            masks.append(m)
+        loss, _, d = O.softmax_loss(acts[-1], y, cfg.loss_weight)
+        losses.append(loss)
+        d = bf(d)
+        for l in reversed(range(cfg.nlayers)):
+            dx, dw, _ = O.fc_bwd(acts[l], bf(W[l]), d, masks[l], cfg.fuse, need_dx=l > 0)
+            W[l] = O.sgd(W[l], dw, cfg.lr)
+            if l > 0:
+                d = bf(dx)
+    return W, losses
+
+
+@pytest.mark.parametrize("fuse", [0, 1, 2, 3])
+def test_trainer_matches_oracle(fuse):
+    from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer
+    from fpga_ai_nic_b200.ops import kernels as K
+    cfg = MLPConfig(sizes=[256, 384, 256, 128], mb=256, fuse=fuse, lr=0.5, loss_weight=1.0)
+    tr = MLPTrainer(cfg)
+    g = torch.Generator().manual_seed(11)
+    x = torch.rand(cfg.mb, cfg.sizes[0], generator=g) * 2 - 1
+    y = torch.randint(0, cfg.sizes[-1], (cfg.mb,), generator=g, dtype=torch.int32)
+    w0 = [tr.buffer("weight", l).cpu().clone() for l in range(cfg.nlayers)]
+    b = [tr.buffer("bias", l).cpu().clone() for l in range(cfg.nlayers)]
+    xb, yd = K.cast_bf16(x.cuda()), y.cuda()
+    losses = []
+    for _ in range(3):
+        tr.step(xb, yd)
+        tr.wait()
+        torch.cuda.synchronize()
+        losses.append(float(tr.loss_dev.item()) / cfg.mb)
+    W, ref_losses = _oracle_steps(cfg, w0, b, x, y, 3)
+    for a, r in zip(losses, ref_losses):
+        assert abs(a - r) <= 2e-2 * abs(r) + 1e-3, (losses, ref_losses)
+    for l in range(cfg.nlayers):
+        upd = (W[l] - w0[l]).norm().clamp_min(1e-12)
+        assert ((tr.buffer("weight", l).cpu() - W[l]).norm() / upd).item() < 0.03
+        # biases are never updated, as in the reference
+        assert torch.equal(tr.buffer("bias", l).cpu(), b[l])
+        # the bf16 shadow the GEMMs read is the rounded master copy
+        assert torch.equal(tr.buffer("shadow", l).cpu(), tr.buffer("weight", l).cpu().bfloat16())
+    assert tr.check_health()["timeouts"] == 0
+    tr.close()
+
+
+def test_checkpoint_resume_is_bit_identical(tmp_path):
+    from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer
+    from fpga_ai_nic_b200.ops import kernels as K
+    from fpga_ai_nic_b200.utils import checkpoint
+    cfg = MLPConfig(sizes=[256, 256, 128], mb=128, lr=0.5, loss_weight=1.0)
+    g = torch.Generator().manual_seed(3)
+    x = K.cast_bf16((torch.rand(cfg.mb, 256, generator=g) - 0.5).cuda())
+    y = torch.randint(0, 128, (cfg.mb,), generator=g, dtype=torch.int32).cuda()
+
+    def run(tr, n):
+        for _ in range(n):
+            tr.step(x, y)
+        tr.wait()
+        torch.cuda.synchronize()
+
+    a = MLPTrainer(cfg)
+    run(a, 2)
+    path = str(tmp_path / "ck.pt")
+    checkpoint.save(a, path, step=2)
+    run(a, 2)
+    want = [a.buffer("weight", l).cpu().clone() for l in range(cfg.nlayers)]
+    a.close()
+    b = MLPTrainer(cfg)
+    assert checkpoint.load(b, path)["step"] == 2
+    run(b, 2)
+    for l in range(cfg.nlayers):
+        assert torch.equal(b.buffer("weight", l).cpu(), want[l])
+    b.close()
+
+
+def test_detailed_profile_phases():
+    from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer
+    from fpga_ai_nic_b200.ops import kernels as K
+    cfg = MLPConfig(sizes=[512, 512, 512], mb=256)
+    tr = MLPTrainer(cfg)
+    x = K.cast_bf16(torch.rand(cfg.mb, 512).cuda())
+    y = torch.zeros(cfg.mb, dtype=torch.int32, device="cuda")
+    tr.step(x, y)
+    tr.profile(True)
+    for _ in range(4):
+        tr.step(x, y)
+    p = tr.profile(False)
+    assert p["steps"] == 4 and p["fwd_fc"] > 0 and p["bwdupd_fc"] > 0 and p["loss"] > 0
+    tr.close()
+
+
+def test_reference_command_line_on_gpu():
+    env = dict(os.environ, DETAILED_PROFILE="1")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "apps", "mlp_train.py"), "5", "256", "3", "A", "32", "32", "32",
+                        "256", "512", "256"], capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0, p.stderr[-2000:]
+    assert re.search(r"^PERFDUMP,BP,[^,]+,1,256,256,512,[0-9.]+,[0-9.]+$", p.stdout, re.M), p.stdout
+    assert "Bwdupd compute FIRST time overlaped" in p.stdout and "loss = " in p.stdout
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "apps", "mlp_train.py"), "3", "128", "0", "F", "32", "32", "32",
+                        "256", "256"], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0 and "PERFDUMP" in p.stdout
