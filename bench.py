@@ -37,6 +37,8 @@ def parse_args():
     ap.add_argument("--codec", default="auto", choices=["auto", "f32", "bfp", "mxfp8", "bf16"])
     ap.add_argument("--algo", default="auto", choices=["auto", "oneshot", "twoshot", "ring"])
     ap.add_argument("--fuse", type=int, default=0)
+    ap.add_argument("--bucket-mb", type=float, default=None,
+                    help="fp32 MiB of gradients per fused all-reduce (0 = per layer; default: 80 from 8 ranks)")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
@@ -124,7 +126,7 @@ def run_ours(args, rank, local, world):
     from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer
     from fpga_ai_nic_b200.ops import kernels as K
     cfg = MLPConfig.reference(args.layers, args.width, args.mb)
-    cfg.fuse, cfg.codec, cfg.algo = args.fuse, args.codec, args.algo
+    cfg.fuse, cfg.codec, cfg.algo, cfg.bucket_mb = args.fuse, args.codec, args.algo, args.bucket_mb
     tr = MLPTrainer(cfg)
     dev = tr.device
     g = torch.Generator().manual_seed(1234 + rank)
@@ -215,6 +217,7 @@ def run_ours(args, rank, local, world):
                    "seq_len": 1, "parallelism": f"dp{world}", "per_rank_batch": cfg.mb, "fuse": cfg.fuse,
                    "optimizer": "sgd lr=0.1 fused into the gradient all-reduce", "master_weights": "fp32",
                    "grad_codec": {0: "f32", 1: "bfp16x8", 2: "mxfp8", 3: "bf16"}[tr.codec], "algo": args.algo,
+                   "grad_bucket_mib": tr.bucket_mb,
                    "l2": "no flush: per-step working set (~0.6 GB of weights, gradients, shadows, activations) exceeds the 126 MB L2"},
         "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"),
                    "reasons": clocks.get("reasons", []), "power_w_max": clocks.get("power_w_max")},

@@ -35,6 +35,7 @@ struct Layer {
   cudaEvent_t updated = nullptr;    // weights + shadow updated (comm stream)
   cudaEvent_t dx_done = nullptr;    // backward-data GEMM finished reading the shadow (main stream)
   uint8_t* cg[2] = {nullptr, nullptr};  // compressed gradient (BFP / MXFP8 frames), symmetric heap, one per step parity
+  size_t slot = 0;               // values reserved in the flat arenas (count rounded up to 1024)
 };
 
 }  // namespace
@@ -61,7 +62,18 @@ struct ainic_mlp {
   unsigned long long launches = 0;
   unsigned long long step_idx = 0;
   bool fuse_compress = false;        // weight-gradient GEMM epilogue emits the wire format directly
+  // All layers' masters / gradients / shadows / compressed gradients live back to back in one
+  // arena each (layer 0 first), so any run of consecutive layers is ONE flat bucket for the fused
+  // all-reduce.  bucket_bytes = fp32 gradient bytes to collect (walking down from the last layer)
+  // before a call is issued; 0 = one call per layer, as in the reference (:754).
+  float* w_arena = nullptr;
+  float* g_arena = nullptr;
+  __nv_bfloat16* wb_arena = nullptr;
+  uint8_t* cg_arena[2] = {nullptr, nullptr};
+  size_t bucket_bytes = 0;
 };
+
+static size_t max_bucket_count(const ainic_mlp* m);
 
 static int fail(const char* what) {
   fprintf(stderr, "ainic_mlp: %s failed: %s\n", what, cudaGetErrorString(cudaGetLastError()));
@@ -115,22 +127,55 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
     TRY_CUDA(cudaMalloc(&m->act[l], (size_t)mb * sizes[l] * 2));
     if (l > 0) TRY_CUDA(cudaMalloc(&m->dact[l], (size_t)mb * sizes[l] * 2));
   }
-  // Symmetric allocations, identical order on every rank.
+  // Symmetric allocations, identical order on every rank: one arena per kind, a layer's slot is
+  // its count rounded up to 1024 values (keeps every slot 4 KiB aligned and frame aligned; the pad
+  // stays zero in gradients and weights, so a multi-layer bucket can run straight across it).
+  size_t total = 0;
+  bool can_fuse = m->fuse_compress;
   for (int l = 0; l < nlayers; ++l) {
     Layer& L = m->layers[l];
     L.in = sizes[l];
     L.out = sizes[l + 1];
     const size_t n = (size_t)L.in * L.out;
-    L.w = static_cast<float*>(ainic_comm_alloc(comm, n * 4, 4096));
-    L.g = static_cast<float*>(ainic_comm_alloc(comm, n * 4, 4096));
-    if (m->fuse_compress && n % 512 == 0 && L.in % 32 == 0) {
-      const size_t cbytes = codec == AINIC_CODEC_BFP ? ainic_bfp_bytes(n) : ainic_mx_bytes(n);
-      L.cg[0] = static_cast<uint8_t*>(ainic_comm_alloc(comm, cbytes, 4096));
-      L.cg[1] = static_cast<uint8_t*>(ainic_comm_alloc(comm, cbytes, 4096));
-      if (!L.cg[0] || !L.cg[1]) return AINIC_ERR_ARG;
+    L.slot = (n + 1023) & ~(size_t)1023;
+    total += L.slot;
+    if (n % 512 || L.in % 32) can_fuse = false;
+  }
+  m->fuse_compress = can_fuse;
+  m->w_arena = static_cast<float*>(ainic_comm_alloc(comm, total * 4, 4096));
+  m->g_arena = static_cast<float*>(ainic_comm_alloc(comm, total * 4, 4096));
+  if (!m->w_arena || !m->g_arena) return AINIC_ERR_ARG;
+  TRY_CUDA(cudaMemset(m->w_arena, 0, total * 4));
+  TRY_CUDA(cudaMemset(m->g_arena, 0, total * 4));
+  TRY_CUDA(cudaMalloc(&m->wb_arena, total * 2));
+  TRY_CUDA(cudaMemset(m->wb_arena, 0, total * 2));
+  const size_t frame_bytes = codec == AINIC_CODEC_BFP ? ainic_bfp_bytes(512) : ainic_mx_bytes(512);
+  if (m->fuse_compress) {
+    for (int i = 0; i < 2; ++i) {
+      m->cg_arena[i] = static_cast<uint8_t*>(ainic_comm_alloc(comm, total / 512 * frame_bytes, 4096));
+      if (!m->cg_arena[i]) return AINIC_ERR_ARG;
+      TRY_CUDA(cudaMemset(m->cg_arena[i], 0, total / 512 * frame_bytes));
     }
-    if (!L.w || !L.g) return AINIC_ERR_ARG;
-    TRY_CUDA(cudaMalloc(&L.wb, n * 2));
+  }
+  {
+    // default bucket size: per layer up to 4 ranks; from 8 ranks the all-reduce queue is the critical
+    // path and its fixed cost per call (three cross-GPU flag exchanges) dominates 16 MiB buckets.
+    const int n = ainic_comm_size(comm);
+    m->bucket_bytes = n >= 8 ? (size_t)80 << 20 : 0;
+    if (const char* e = getenv("AINIC_BUCKET_MB")) m->bucket_bytes = (size_t)(atof(e) * 1048576.0);
+  }
+  TRY(ainic_comm_reserve(comm, max_bucket_count(m)));
+  size_t off = 0;
+  for (int l = 0; l < nlayers; ++l) {
+    Layer& L = m->layers[l];
+    L.w = m->w_arena + off;
+    L.g = m->g_arena + off;
+    L.wb = m->wb_arena + off;
+    if (m->fuse_compress) {
+      L.cg[0] = m->cg_arena[0] + off / 512 * frame_bytes;
+      L.cg[1] = m->cg_arena[1] + off / 512 * frame_bytes;
+    }
+    off += L.slot;
     TRY_CUDA(cudaMalloc(&L.bias, (size_t)L.out * 4));
     TRY_CUDA(cudaMalloc(&L.dbias, (size_t)L.out * 4));
     TRY_CUDA(cudaMemset(L.bias, 0, (size_t)L.out * 4));
@@ -148,9 +193,10 @@ extern "C" int ainic_mlp_destroy(ainic_mlp_t* m) {
   if (!m) return AINIC_ERR_ARG;
   cudaDeviceSynchronize();
   for (auto& L : m->layers) {
-    cudaFree(L.wb); cudaFree(L.bias); cudaFree(L.dbias); cudaFree(L.mask);
+    cudaFree(L.bias); cudaFree(L.dbias); cudaFree(L.mask);
     cudaEventDestroy(L.dy_ready); cudaEventDestroy(L.dw_ready); cudaEventDestroy(L.updated); cudaEventDestroy(L.dx_done);
   }
+  cudaFree(m->wb_arena);
   for (auto p : m->act) cudaFree(p);
   for (auto p : m->dact) cudaFree(p);
   cudaFree(m->loss_sum);
@@ -189,6 +235,27 @@ extern "C" int ainic_mlp_sync_shadows(ainic_mlp_t* m, void* stream) {
 }
 
 extern "C" unsigned long long ainic_mlp_launches(ainic_mlp_t* m) { return m ? m->launches : 0; }
+// Largest bucket (in values, arena pads included) the current bucket size produces.
+static size_t max_bucket_count(const ainic_mlp* m) {
+  size_t best = 0, count = 0, pending = 0;
+  for (int l = m->nlayers - 1; l >= 0; --l) {
+    const Layer& L = m->layers[l];
+    count += L.slot;
+    pending += (size_t)L.in * L.out * 4;
+    if (l > 0 && pending < m->bucket_bytes) continue;
+    if (count > best) best = count;
+    count = pending = 0;
+  }
+  return best;
+}
+// Gradient bucket size in fp32 bytes (0 = one all-reduce per layer).  Takes effect at the next step;
+// collective (every rank must set the same value at the same point).
+extern "C" int ainic_mlp_set_bucket_bytes(ainic_mlp_t* m, size_t bytes) {
+  if (!m) return AINIC_ERR_ARG;
+  m->bucket_bytes = bytes;
+  return ainic_comm_reserve(m->comm, max_bucket_count(m));
+}
+extern "C" size_t ainic_mlp_bucket_bytes(ainic_mlp_t* m) { return m ? m->bucket_bytes : 0; }
 extern "C" void* ainic_mlp_loss_ptr(ainic_mlp_t* m) { return m ? m->loss_sum : nullptr; }
 
 static int forward(ainic_mlp* m, cudaStream_t s, bool wait_updates) {
@@ -242,6 +309,8 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
     m->launches++;
   }
   if (m->profile) TRY_CUDA(cudaEventRecord(m->prof[2], s));
+  int hi = Ln - 1;             // top layer of the bucket being collected
+  size_t pending_bytes = 0;
   for (int l = Ln - 1; l >= 0; --l) {
     Layer& L = m->layers[l];
     // dact[l+1] is final here (for ReLU layers the mask was already applied by the producer below)
@@ -274,14 +343,22 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
       m->launches++;
       TRY_CUDA(cudaEventRecord(L.dx_done, s));
     }
-    // --- fused all-reduce + SGD of bucket l on the comm stream
-    TRY_CUDA(cudaStreamWaitEvent(m->comm_stream, L.dw_ready, 0));
-    if (l > 0) TRY_CUDA(cudaStreamWaitEvent(m->comm_stream, L.dx_done, 0));  // shadow is rewritten below
+    // --- fused all-reduce + SGD on the comm stream, once the bucket that ends at layer l is full
+    pending_bytes += (size_t)L.in * L.out * 4;
+    if (l > 0 && pending_bytes < m->bucket_bytes) continue;
+    const int lo = l;                                   // bucket = layers lo .. hi, contiguous in the arenas
+    TRY_CUDA(cudaStreamWaitEvent(m->comm_stream, L.dw_ready, 0));   // wgrad stream is in order: covers lo .. hi
+    // the shadows of lo .. hi are rewritten below; the last backward-data GEMM that reads one of them
+    // is layer max(lo,1)'s (main stream is in order)
+    if (hi > 0) TRY_CUDA(cudaStreamWaitEvent(m->comm_stream, m->layers[lo > 0 ? lo : 1].dx_done, 0));
+    size_t count = 0;
+    for (int k = lo; k < hi; ++k) count += m->layers[k].slot;
+    count += (size_t)m->layers[hi].in * m->layers[hi].out;
     ainic_allreduce_args_t a{};
     a.grad = L.g;
     a.weight = L.w;
     a.weight_bf16 = L.wb;
-    a.count = (size_t)L.in * L.out;
+    a.count = count;
     a.lr = m->lr;
     a.codec = m->codec;
     a.bfp_mode = m->bfp_mode;
@@ -290,7 +367,9 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
     a.grad_compressed = cg;
     TRY(ainic_allreduce_fused(m->comm, &a, m->comm_stream));
     m->launches++;
-    TRY_CUDA(cudaEventRecord(L.updated, m->comm_stream));
+    for (int k = lo; k <= hi; ++k) TRY_CUDA(cudaEventRecord(m->layers[k].updated, m->comm_stream));
+    hi = l - 1;
+    pending_bytes = 0;
   }
   m->first_step = false;
   m->step_idx++;

@@ -182,8 +182,9 @@ __device__ __forceinline__ void reduce_tail_f32(const RankCtx& c, size_t f, floa
 // ------------------------------------------------------------------------------------------ two frames per iteration
 // The per-frame work is a chain of dependent memory operations (peer load ~2-3 us over NVLink ->
 // decode -> weight load -> store), and an 8-warp CTA has little thread-level parallelism to hide it
-// (measured: 49 us for a 16 MiB bucket at 2 ranks, ~4x the HBM time).  The hot loops therefore
-// handle TWO full frames per warp iteration and issue the loads of both before consuming either.
+// (measured: 49 us for a 16 MiB bucket at 2 ranks, ~4x the HBM time).  The compression loop
+// therefore handles TWO full frames per warp iteration; the reduce / gather loops are software
+// pipelined (reduce_stream / gather_stream below).
 // Only the last frame of a bucket can be partial (count % 512 != 0); it is kept out of the hot
 // loops and handled once per phase by the warp that owns it, through the predicated slow path.
 __device__ __forceinline__ bool frame_full(const RankCtx& c, size_t f) { return (f + 1) * kFrameVals <= c.count; }
@@ -193,63 +194,6 @@ template <int CODEC, int MODE>
 __device__ __forceinline__ const uint8_t* reduce_src(const RankCtx& c, size_t parity_off, int p, size_t f) {
   return CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f * 2048
                     : c.stage_c[p] + parity_off + f * FrameCodec<CODEC, MODE>::kBytes;
-}
-
-// acc0/acc1 = sum over ranks (rank order) of frames f0/f1; frame 1 is skipped when !has1 (warp-uniform).
-template <int CODEC, int MODE>
-__device__ __forceinline__ void reduce_pair(const RankCtx& c, size_t parity_off, size_t f0, size_t f1, bool has1,
-                                            float (&acc0)[16], float (&acc1)[16], int lane) {
-  using FC = FrameCodec<CODEC, MODE>;
-  constexpr int PB = sizeof(typename FC::Raw) > 32 ? 1 : 4;  // peers per batch: bounded by registers
-  const int N = c.nranks;
-  float v[16];
-#pragma unroll 1
-  for (int p0 = 0; p0 < N; p0 += PB) {
-    typename FC::Raw r0[PB], r1[PB];
-#pragma unroll
-    for (int k = 0; k < PB; ++k)
-      if (p0 + k < N) {
-        FC::load(reduce_src<CODEC, MODE>(c, parity_off, p0 + k, f0), r0[k], lane);
-        if (has1) FC::load(reduce_src<CODEC, MODE>(c, parity_off, p0 + k, f1), r1[k], lane);
-      }
-#pragma unroll
-    for (int k = 0; k < PB; ++k)
-      if (p0 + k < N) {
-        FC::unpack(r0[k], v, lane);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) acc0[i] = (p0 + k == 0) ? v[i] : acc0[i] + v[i];
-        if (has1) {
-          FC::unpack(r1[k], v, lane);
-#pragma unroll
-          for (int i = 0; i < 16; ++i) acc1[i] = (p0 + k == 0) ? v[i] : acc1[i] + v[i];
-        }
-      }
-  }
-}
-
-// w = fmaf(-lr, g, w) (+ shadow, + reduced-gradient output) on one or two FULL frames; both weight
-// frames are loaded before either is updated.
-__device__ __forceinline__ void apply_pair(const RankCtx& c, size_t f0, size_t f1, bool has1, const float (&g0)[16],
-                                           const float (&g1)[16], int lane) {
-  if (c.grad_out) {
-    frame_store_f32(c.grad_out + f0 * kFrameVals, kFrameVals, g0, lane);
-    if (has1) frame_store_f32(c.grad_out + f1 * kFrameVals, kFrameVals, g1, lane);
-  }
-  if (c.weight) {
-    float w0[16], w1[16];
-    frame_load_f32(c.weight + f0 * kFrameVals, kFrameVals, w0, lane);
-    if (has1) frame_load_f32(c.weight + f1 * kFrameVals, kFrameVals, w1, lane);
-#pragma unroll
-    for (int i = 0; i < 16; ++i) w0[i] = fmaf(-c.lr, g0[i], w0[i]);
-    frame_store_f32(c.weight + f0 * kFrameVals, kFrameVals, w0, lane);
-    if (c.wshadow) frame_store_bf16(c.wshadow + f0 * kFrameVals, kFrameVals, w0, lane);
-    if (has1) {
-#pragma unroll
-      for (int i = 0; i < 16; ++i) w1[i] = fmaf(-c.lr, g1[i], w1[i]);
-      frame_store_f32(c.weight + f1 * kFrameVals, kFrameVals, w1, lane);
-      if (c.wshadow) frame_store_bf16(c.wshadow + f1 * kFrameVals, kFrameVals, w1, lane);
-    }
-  }
 }
 
 // Compress up to two full frames of the local gradient into stage C.
@@ -262,6 +206,132 @@ __device__ __forceinline__ void compress_pair(const RankCtx& c, size_t parity_of
   if (has1) frame_load_f32(c.grad + f1 * kFrameVals, kFrameVals, b, lane);
   FC::encode(a, dst + f0 * FC::kBytes, lane);
   if (has1) FC::encode(b, dst + f1 * FC::kBytes, lane);
+}
+
+// ------------------------------------------------------------------------------------------ software-pipelined streams
+// Measured on the pair loops above at 8 ranks (16 MiB bucket): reduce phase 38 us, gather phase 23 us
+// for ~10 us of wire + HBM time.  A warp's iterations were a serial chain: peer frames (NVLink
+// round trip, ~3 us) -> decode -> weight frame (HBM round trip, ~1 us) -> store -> next iteration.
+// The streams below keep the next batch of peer frames AND the weight frame of the current
+// iteration in flight while the current batch is consumed, so a warp pays max(remote, local)
+// instead of their sum, and nothing waits between iterations.
+
+// w = fmaf(-lr, g, w) on one FULL frame whose weights were requested earlier.
+__device__ __forceinline__ void apply_full_w(const RankCtx& c, size_t f, const float (&g)[16], float (&w)[16], int lane) {
+  if (c.grad_out) frame_store_f32(c.grad_out + f * kFrameVals, kFrameVals, g, lane);
+  if (c.weight) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = fmaf(-c.lr, g[i], w[i]);
+    frame_store_f32(c.weight + f * kFrameVals, kFrameVals, w, lane);
+    if (c.wshadow) frame_store_bf16(c.wshadow + f * kFrameVals, kFrameVals, w, lane);
+  }
+}
+
+// Reduce frames base + j, j = first, first + step, ... < lim over all ranks in rank order and hand
+// each sum to sink(j, acc, w) together with the frame's (already loaded) weights.  Peers are read in
+// batches of PB; batch k + 1 (possibly of the next frame) is requested before batch k is decoded.
+template <int CODEC, int MODE, class Sink>
+__device__ __forceinline__ void reduce_stream(const RankCtx& c, size_t parity_off, size_t base, size_t first, size_t step,
+                                              size_t lim, int lane, Sink sink) {
+  using FC = FrameCodec<CODEC, MODE>;
+  using Raw = typename FC::Raw;
+  constexpr int PB = sizeof(Raw) > 32 ? 2 : 4;
+  const int N = c.nranks;
+  const int nb = (N + PB - 1) / PB;
+  if (first >= lim) return;
+  Raw cur[PB], nxt[PB];
+  size_t j = first;
+  int b = 0;
+#pragma unroll
+  for (int k = 0; k < PB; ++k)
+    if (k < N) FC::load(reduce_src<CODEC, MODE>(c, parity_off, k, base + j), cur[k], lane);
+  float acc[16], w[16], v[16];
+#pragma unroll 1
+  for (;;) {
+    size_t nj = j;
+    int nbq = b + 1;
+    if (nbq == nb) { nbq = 0; nj = j + step; }
+    const bool more = nj < lim;
+    if (more) {
+#pragma unroll
+      for (int k = 0; k < PB; ++k)
+        if (nbq * PB + k < N) FC::load(reduce_src<CODEC, MODE>(c, parity_off, nbq * PB + k, base + nj), nxt[k], lane);
+    }
+    if (b == 0 && c.weight) frame_load_f32(c.weight + (base + j) * kFrameVals, kFrameVals, w, lane);
+#pragma unroll
+    for (int k = 0; k < PB; ++k)
+      if (b * PB + k < N) {  // warp-uniform
+        FC::unpack(cur[k], v, lane);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc[i] = (b == 0 && k == 0) ? v[i] : acc[i] + v[i];
+      }
+    if (b == nb - 1) sink(j, acc, w);
+    if (!more) break;
+#pragma unroll
+    for (int k = 0; k < PB; ++k) cur[k] = nxt[k];
+    j = nj;
+    b = nbq;
+  }
+}
+
+// Two-shot gather: apply every other rank's published (reduced) shard.  A warp's (peer, frame) items
+// form one flat sequence; they are fetched G at a time, group k + 1 while group k is applied, and
+// the weights of item i + 1 are requested before item i is decoded.
+template <int CODEC, int MODE>
+__device__ __forceinline__ void gather_stream(const RankCtx& c, size_t shard, size_t full, size_t first, size_t step, int lane) {
+  using FC = FrameCodec<CODEC, MODE>;
+  using Raw = typename FC::Raw;
+  constexpr int G = sizeof(Raw) > 32 ? 1 : 4;
+  constexpr uint32_t kNone = 0xFFFFFFFFu;
+  const int N = c.nranks;
+  auto lim_of = [&](int d) -> size_t {
+    const size_t lo = (size_t)((c.rank + d) % N) * shard;
+    return full <= lo ? 0 : (full - lo < shard ? full - lo : shard);
+  };
+  int dp = 1;         // peers are visited staggered (rank + 1, rank + 2, ...) so the links are used evenly
+  size_t j = first;
+  while (dp < N && j >= lim_of(dp)) ++dp;
+  Raw cur[G], nxt[G];
+  uint32_t cf[G], nf[G];
+  auto fetch = [&](Raw (&r)[G], uint32_t (&fi)[G]) {
+#pragma unroll
+    for (int k = 0; k < G; ++k) {
+      if (dp < N) {
+        const int p = (c.rank + dp) % N;
+        const size_t f = (size_t)p * shard + j;
+        fi[k] = (uint32_t)f;
+        FC::load(CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f * 2048 : c.stage_d[p] + j * FC::kBytes, r[k], lane);
+        j += step;
+        while (dp < N && j >= lim_of(dp)) { ++dp; j = first; }
+      } else {
+        fi[k] = kNone;
+      }
+    }
+  };
+  fetch(cur, cf);
+  float wa[16], wb[16], g[16];
+  if (cf[0] != kNone && c.weight) frame_load_f32(c.weight + (size_t)cf[0] * kFrameVals, kFrameVals, wa, lane);
+#pragma unroll 1
+  while (cf[0] != kNone) {
+    fetch(nxt, nf);
+#pragma unroll
+    for (int k = 0; k < G; ++k) {
+      if (cf[k] != kNone) {  // warp-uniform; valid items are a prefix of the group
+        float (&wc)[16] = (k & 1) ? wb : wa;
+        float (&wn)[16] = (k & 1) ? wa : wb;
+        const uint32_t nfi = (k + 1 < G) ? cf[(k + 1) % G] : nf[0];
+        if (nfi != kNone && c.weight) frame_load_f32(c.weight + (size_t)nfi * kFrameVals, kFrameVals, wn, lane);
+        FC::unpack(cur[k], g, lane);
+        apply_full_w(c, cf[k], g, wc, lane);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < G; ++k) { cur[k] = nxt[k]; cf[k] = nf[k]; }
+    if (G & 1) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) wa[i] = wb[i];
+    }
+  }
 }
 
 // ---- slow path for the one partial frame of a bucket (never inlined into the hot loops)
@@ -321,14 +391,8 @@ __device__ void oneshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
     __syncthreads();
   }
   mark_phase(ws, 0);
-#pragma unroll 1
-  for (size_t f0 = first; f0 < full; f0 += 2 * step) {
-    const size_t f1 = f0 + step;
-    const bool has1 = f1 < full;
-    float acc0[16], acc1[16];
-    reduce_pair<CODEC, MODE>(c, parity_off, f0, f1, has1, acc0, acc1, lane);
-    apply_pair(c, f0, f1, has1, acc0, acc1, lane);
-  }
+  reduce_stream<CODEC, MODE>(c, parity_off, 0, first, step, full, lane,
+                             [&](size_t f, float (&acc)[16], float (&w)[16]) { apply_full_w(c, f, acc, w, lane); });
   if (own_tail) tail_reduce_apply<CODEC, MODE>(c, parity_off, full, false, 0, lane);
   if (CODEC == 0 && N > 1) {  // peers read my gradient in place: do not return before they are done
     signal_all(c, 2, cta, c.epoch);
@@ -377,26 +441,16 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   // phase 1: reduce my shard from every rank, publish it re-encoded, update my shard's weights
   {
     const size_t base = (size_t)c.rank * shard, lim = shard_full(c.rank);
-#pragma unroll 1
-    for (size_t j0 = first; j0 < lim; j0 += 2 * step) {
-      const size_t j1 = j0 + step, f0 = base + j0, f1 = base + j1;
-      const bool has1 = j1 < lim;
-      float acc0[16], acc1[16];
-      reduce_pair<CODEC, MODE>(c, parity_off, f0, f1, has1, acc0, acc1, lane);
+    reduce_stream<CODEC, MODE>(c, parity_off, base, first, step, lim, lane, [&](size_t j, float (&acc)[16], float (&w)[16]) {
       if (CODEC == 0) {
-        if (N > 1) {  // in place: peers pull the reduced shard out of my gradient buffer
-          frame_store_f32(c.grad + f0 * kFrameVals, kFrameVals, acc0, lane);
-          if (has1) frame_store_f32(c.grad + f1 * kFrameVals, kFrameVals, acc1, lane);
-        }
+        // in place: peers pull the reduced shard out of my gradient buffer
+        if (N > 1) frame_store_f32(c.grad + (base + j) * kFrameVals, kFrameVals, acc, lane);
       } else {
         // publish, then apply exactly what the peers will decode (fixes SURVEY D11)
-        uint8_t* d0 = c.stage_d[c.rank] + j0 * FC::kBytes;
-        uint8_t* d1 = c.stage_d[c.rank] + j1 * FC::kBytes;
-        frame_encode_rt<CODEC, MODE>(acc0, d0, lane);
-        if (has1) frame_encode_rt<CODEC, MODE>(acc1, d1, lane);
+        frame_encode_rt<CODEC, MODE>(acc, c.stage_d[c.rank] + j * FC::kBytes, lane);
       }
-      apply_pair(c, f0, f1, has1, acc0, acc1, lane);
-    }
+      apply_full_w(c, base + j, acc, w, lane);
+    });
     if (own_tail && ts == c.rank) tail_reduce_apply<CODEC, MODE>(c, parity_off, full, true, tj, lane);
   }
   if (N == 1) return;
@@ -404,23 +458,8 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   wait_all(c, 1, cta, c.epoch, ws);
   mark_phase(ws, 1);
   // phase 2: pull every other rank's reduced shard
-  for (int dp = 1; dp < N; ++dp) {
-    const int p = (c.rank + dp) % N;  // stagger the peers so the links are used evenly
-    const size_t base = (size_t)p * shard, lim = shard_full(p);
-#pragma unroll 1
-    for (size_t j0 = first; j0 < lim; j0 += 2 * step) {
-      const size_t j1 = j0 + step, f0 = base + j0, f1 = base + j1;
-      const bool has1 = j1 < lim;
-      typename FC::Raw r0, r1;
-      float g0[16], g1[16];
-      FC::load(CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f0 * 2048 : c.stage_d[p] + j0 * FC::kBytes, r0, lane);
-      if (has1) FC::load(CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f1 * 2048 : c.stage_d[p] + j1 * FC::kBytes, r1, lane);
-      FC::unpack(r0, g0, lane);
-      if (has1) FC::unpack(r1, g1, lane);
-      apply_pair(c, f0, f1, has1, g0, g1, lane);
-    }
-    if (own_tail && ts == p) tail_gather_apply<CODEC, MODE>(c, p, full, tj, lane);
-  }
+  gather_stream<CODEC, MODE>(c, shard, full, first, step, lane);
+  if (own_tail && ts != c.rank) tail_gather_apply<CODEC, MODE>(c, ts, full, tj, lane);
   if (CODEC == 0) {
     signal_all(c, 2, cta, c.epoch);
     wait_all(c, 2, cta, c.epoch, ws);

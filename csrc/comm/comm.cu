@@ -241,6 +241,13 @@ static int ensure_staging(ainic_comm* c, size_t count) {
 
 extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_allreduce_args_t* a);
 
+// Size the internal staging for calls of up to `count` values now (same call on every rank), so the
+// first large bucket does not abandon a smaller staging area inside the grow-only heap.
+extern "C" int ainic_comm_reserve(ainic_comm_t* c, size_t count) {
+  if (!c || count == 0) return AINIC_ERR_ARG;
+  return ensure_staging(c, count);
+}
+
 extern "C" int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args_t* a, void* stream) {
   if (!c || !a || !a->grad || a->count == 0) return AINIC_ERR_ARG;
   if (!c->connected) { set_error("communicator not connected"); return AINIC_ERR_ARG; }

@@ -165,6 +165,10 @@ def cuda() -> C.CDLL:
     lib.ainic_mlp_profile.argtypes = [vp, C.c_int, C.POINTER(C.c_double)]
     lib.ainic_mlp_launches.restype = C.c_ulonglong
     lib.ainic_mlp_launches.argtypes = [vp]
+    lib.ainic_mlp_set_bucket_bytes.restype = C.c_int
+    lib.ainic_mlp_set_bucket_bytes.argtypes = [vp, C.c_size_t]
+    lib.ainic_mlp_bucket_bytes.restype = C.c_size_t
+    lib.ainic_mlp_bucket_bytes.argtypes = [vp]
     lib.ainic_mlp_loss_ptr.restype = vp
     lib.ainic_mlp_loss_ptr.argtypes = [vp]
     for fn, args, res in _NIC_SIGS:

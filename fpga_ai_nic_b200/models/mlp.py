@@ -8,6 +8,7 @@ reference run (10 x 2048 x 2048, 1792 samples per rank, fuse 0; sw/run.sh:16).
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, field
 
 import torch
@@ -30,6 +31,8 @@ class MLPConfig:
     algo: str = "auto"
     seed: int = 1                                              # libxsmm_rng_set_seed(1), :273
     init_scale: float = 1.0                                    # multiplies the reference init (wide layers need < 1)
+    bucket_mb: float | None = None                             # fp32 MiB of gradients per all-reduce call; 0 = per
+                                                               # layer (reference, :754); None = 80 from 8 ranks, else 0
 
     @staticmethod
     def reference(nlayers: int = 10, width: int = 2048, mb: int = 1792) -> "MLPConfig":
@@ -49,10 +52,20 @@ class MLPConfig:
     def param_count(self) -> int:
         return sum(self.sizes[l] * self.sizes[l + 1] for l in range(self.nlayers))
 
-    def heap_bytes(self) -> int:
-        p = self.param_count()
+    def resolved_bucket_mb(self, world: int) -> float:
+        if self.bucket_mb is not None:
+            return float(self.bucket_mb)
+        if os.environ.get("AINIC_BUCKET_MB"):
+            return float(os.environ["AINIC_BUCKET_MB"])
+        return 80.0 if world >= 8 else 0.0
+
+    def heap_bytes(self, world: int = 8) -> int:
+        p = self.param_count() + 1024 * self.nlayers
         biggest = max(self.sizes[l] * self.sizes[l + 1] for l in range(self.nlayers))
-        frames = (biggest + 511) // 512
+        # a bucket closes once it holds >= bucket_mb, so it is smaller than bucket_mb + the biggest layer;
+        # sized for the default AND an explicit setting because the staging area only grows
+        bucket = int(max(self.resolved_bucket_mb(world), 80.0 if world >= 8 else 0.0) * (1 << 20) / 4)
+        frames = (min(p, bucket + biggest) + 1023) // 512 + (biggest + 511) // 512
         # fp32 weights + fp32 gradients, two compressed-gradient buffers per layer (GEMM epilogue output),
         # the communicator's staging for the largest bucket, slack for alignment
         return p * 8 + p * 3 + frames * (2 * 1024 + 2 * 2048) + (8 << 20) + self.nlayers * 32768
@@ -62,7 +75,11 @@ class MLPTrainer:
     def __init__(self, cfg: MLPConfig, comm: Communicator | None = None):
         self.cfg = cfg
         self.lib = N.cuda()
-        self.comm = comm if comm is not None else Communicator(cfg.heap_bytes())
+        if comm is None:
+            import torch.distributed as dist
+            world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+            comm = Communicator(cfg.heap_bytes(world))
+        self.comm = comm
         self.world = self.comm.world_size
         codec = cfg.codec
         if codec == "auto":
@@ -74,6 +91,8 @@ class MLPTrainer:
         N.check(self.lib.ainic_mlp_create(C.byref(h), self.comm.handle, cfg.nlayers, sizes, cfg.mb, cfg.fuse, cfg.lr,
                                           cfg.loss_weight, self.codec, cfg.bfp_mode, self.algo), "mlp_create")
         self.handle = h
+        if cfg.bucket_mb is not None:
+            self.set_bucket_mb(cfg.bucket_mb)
         self.device = self.comm.device
         self.loss_dev = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._views: dict = {}
@@ -130,6 +149,15 @@ class MLPTrainer:
         N.check(self.lib.ainic_mlp_step(self.handle, x.data_ptr(), labels.data_ptr(),
                                         self.loss_dev.data_ptr() if want_loss else None, N.stream_ptr()), "mlp_step")
         return self.loss_dev if want_loss else None
+
+    def set_bucket_mb(self, mb: float) -> None:
+        """Gradient bucket size (fp32 MiB collected from the last layer down before one fused
+        all-reduce is issued; 0 = one call per layer).  Collective: same value on every rank."""
+        N.check(self.lib.ainic_mlp_set_bucket_bytes(self.handle, int(mb * (1 << 20))), "mlp_set_bucket_bytes")
+
+    @property
+    def bucket_mb(self) -> float:
+        return self.lib.ainic_mlp_bucket_bytes(self.handle) / float(1 << 20)
 
     def wait(self) -> None:
         """Make the current stream wait for all outstanding weight updates (reference: wait(), :157-180)."""

@@ -124,6 +124,9 @@ typedef struct ainic_allreduce_args {
 } ainic_allreduce_args_t;
 /* Fused compress -> (peer pull) -> fp32 reduce -> decompress -> SGD, one kernel launch on stream. */
 int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args_t* args, void* stream);
+/* Pre-size the communicator's staging for calls of up to `count` values (collective: same call on
+ * every rank).  Optional - staging also grows on demand, but growth abandons the old area. */
+int ainic_comm_reserve(ainic_comm_t* c, size_t count);
 /* Device-side phase counters of the last completed fused all-reduce (ns from %globaltimer):
  * [0] total busy, [1] waiting for peers, [2] launches.  The analogue of lpbk_latency /
  * stall_* (hw/all_reduce.sv:92-98, :892-1072). */
@@ -190,6 +193,12 @@ int ainic_mlp_wait_updates(ainic_mlp_t* m, void* stream);
  * last weight update; returns the number of profiled steps.  Profiling serialises the step at its end. */
 unsigned long long ainic_mlp_profile(ainic_mlp_t* m, int enable, double out_ms[4]);
 unsigned long long ainic_mlp_launches(ainic_mlp_t* m);
+/* Gradient bucketing: consecutive layers are contiguous in memory, so one fused all-reduce can cover
+ * several.  bytes = fp32 gradient bytes to collect (from the last layer down) before a call is
+ * issued; 0 = one call per layer like the reference (sw/mlp_mpi_example_f32.cpp:754).  Default: 0 up
+ * to 4 ranks, 80 MiB from 8 ranks; AINIC_BUCKET_MB overrides at create time. */
+int ainic_mlp_set_bucket_bytes(ainic_mlp_t* m, size_t bytes);
+size_t ainic_mlp_bucket_bytes(ainic_mlp_t* m);
 void* ainic_mlp_loss_ptr(ainic_mlp_t* m);
 
 /* ---------------------------------------------------------------- NIC-style command interface (C1a, C17)

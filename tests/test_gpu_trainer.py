@@ -125,3 +125,30 @@ def test_reference_command_line_on_gpu():
     p = subprocess.run([sys.executable, os.path.join(ROOT, "apps", "mlp_train.py"), "3", "128", "0", "F", "32", "32", "32",
                         "256", "256"], capture_output=True, text=True, timeout=300)
     assert p.returncode == 0 and "PERFDUMP" in p.stdout
+
+
+@pytest.mark.parametrize("bucket_mb", [0.2, 1000.0])
+def test_bucketed_allreduce_same_bits_as_per_layer(bucket_mb):
+    """Several layers per fused call (layer slots are padded to 1024 values inside one arena; 264 x 264
+    is not a multiple of 1024, so the bucket runs across zero padding) == one call per layer (:754)."""
+    from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer
+    from fpga_ai_nic_b200.ops import kernels as K
+    sizes = [264, 264, 136, 264, 128]
+    g = torch.Generator().manual_seed(5)
+    x = K.cast_bf16((torch.rand(128, sizes[0], generator=g) - 0.5).cuda())
+    y = torch.randint(0, sizes[-1], (128,), generator=g, dtype=torch.int32).cuda()
+    out = []
+    for mb in (0.0, bucket_mb):
+        tr = MLPTrainer(MLPConfig(sizes=sizes, mb=128, fuse=2, lr=0.5, loss_weight=1.0, bucket_mb=mb))
+        assert abs(tr.bucket_mb - mb) < 1e-6
+        n0 = tr.comm.counters()["launches"]
+        for _ in range(3):
+            tr.step(x, y)
+        tr.wait()
+        torch.cuda.synchronize()
+        calls = tr.comm.counters()["launches"] - n0
+        out.append(([tr.buffer("weight", l).cpu().clone() for l in range(4)], calls))
+        tr.close()
+    assert out[0][1] == 12 and out[1][1] == (3 if bucket_mb > 100 else 6)
+    for a, b in zip(out[0][0], out[1][0]):
+        assert torch.equal(a, b)
