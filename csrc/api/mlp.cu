@@ -62,6 +62,7 @@ struct ainic_mlp {
   unsigned long long launches = 0;
   unsigned long long step_idx = 0;
   bool fuse_compress = false;        // weight-gradient GEMM epilogue emits the wire format directly
+  bool fuse_scatter = false;         // ... and stores every frame into its owner's inbox (GEMM -> reduce-scatter)
   // All layers' masters / gradients / shadows / compressed gradients live back to back in one
   // arena each (layer 0 first), so any run of consecutive layers is ONE flat bucket for the fused
   // all-reduce.  bucket_bytes = fp32 gradient bytes to collect (walking down from the last layer)
@@ -110,9 +111,12 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
   // AINIC_FUSE_COMPRESS=0/1 overrides.
   {
     const int n = ainic_comm_size(comm);
-    bool on = n >= 8;
-    if (const char* e = getenv("AINIC_FUSE_COMPRESS")) on = atoi(e) == 1;
-    m->fuse_compress = on && n > 1 && (codec == AINIC_CODEC_BFP || codec == AINIC_CODEC_MXFP8);
+    int mode = n >= 8 ? 1 : 0;
+    if (const char* e = getenv("AINIC_FUSE_COMPRESS")) mode = atoi(e);
+    m->fuse_compress = mode >= 1 && n > 1 && (codec == AINIC_CODEC_BFP || codec == AINIC_CODEC_MXFP8);
+    // AINIC_FUSE_COMPRESS=2: the epilogue also performs the reduce-scatter's data movement - each frame
+    // is stored into the inbox of the rank that owns it, over NVLink, while the GEMM is still running.
+    m->fuse_scatter = m->fuse_compress && mode == 2;
   }
   m->layers.resize(nlayers);
   m->act.resize(nlayers + 1);
@@ -150,11 +154,16 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
   TRY_CUDA(cudaMalloc(&m->wb_arena, total * 2));
   TRY_CUDA(cudaMemset(m->wb_arena, 0, total * 2));
   const size_t frame_bytes = codec == AINIC_CODEC_BFP ? ainic_bfp_bytes(512) : ainic_mx_bytes(512);
+  m->fuse_scatter = m->fuse_scatter && m->fuse_compress;
+  // scatter mode: a bucket of F frames is laid out as nranks rows of ceil(F / nranks) frames, up to
+  // nranks - 1 frames more than F; 8 spare frames per layer keep the next bucket's region clear
+  const size_t gap = m->fuse_scatter ? AINIC_MAX_RANKS : 0;
   if (m->fuse_compress) {
+    const size_t cg_frames = total / 512 + gap * nlayers;
     for (int i = 0; i < 2; ++i) {
-      m->cg_arena[i] = static_cast<uint8_t*>(ainic_comm_alloc(comm, total / 512 * frame_bytes, 4096));
+      m->cg_arena[i] = static_cast<uint8_t*>(ainic_comm_alloc(comm, cg_frames * frame_bytes, 4096));
       if (!m->cg_arena[i]) return AINIC_ERR_ARG;
-      TRY_CUDA(cudaMemset(m->cg_arena[i], 0, total / 512 * frame_bytes));
+      TRY_CUDA(cudaMemset(m->cg_arena[i], 0, cg_frames * frame_bytes));
     }
   }
   {
@@ -172,8 +181,8 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
     L.g = m->g_arena + off;
     L.wb = m->wb_arena + off;
     if (m->fuse_compress) {
-      L.cg[0] = m->cg_arena[0] + off / 512 * frame_bytes;
-      L.cg[1] = m->cg_arena[1] + off / 512 * frame_bytes;
+      L.cg[0] = m->cg_arena[0] + (off / 512 + gap * l) * frame_bytes;
+      L.cg[1] = m->cg_arena[1] + (off / 512 + gap * l) * frame_bytes;
     }
     off += L.slot;
     TRY_CUDA(cudaMalloc(&L.bias, (size_t)L.out * 4));
@@ -309,8 +318,25 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
     m->launches++;
   }
   if (m->profile) TRY_CUDA(cudaEventRecord(m->prof[2], s));
-  int hi = Ln - 1;             // top layer of the bucket being collected
-  size_t pending_bytes = 0;
+  // bucket plan (walk down from the last layer): blo[l] / bhi[l] = lowest / highest layer of l's bucket
+  std::vector<int> blo(Ln), bhi(Ln);
+  {
+    int top = Ln - 1;
+    size_t pend = 0;
+    for (int l = Ln - 1; l >= 0; --l) {
+      pend += (size_t)m->layers[l].in * m->layers[l].out * 4;
+      if (l > 0 && pend < m->bucket_bytes) continue;
+      for (int k = l; k <= top; ++k) { blo[k] = l; bhi[k] = top; }
+      top = l - 1;
+      pend = 0;
+    }
+  }
+  auto bucket_count = [&](int lo, int hi) {
+    size_t count = 0;
+    for (int k = lo; k < hi; ++k) count += m->layers[k].slot;
+    return count + (size_t)m->layers[hi].in * m->layers[hi].out;
+  };
+  const int nranks = ainic_comm_size(m->comm), rank = ainic_comm_rank(m->comm);
   for (int l = Ln - 1; l >= 0; --l) {
     Layer& L = m->layers[l];
     // dact[l+1] is final here (for ReLU layers the mask was already applied by the producer below)
@@ -320,10 +346,23 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
     ainic_gemm_epilogue_t we{};
     we.alpha = 1.0f;
     uint8_t* cg = L.cg[m->step_idx & 1];   // null unless the epilogue emits the wire format
+    ainic_gemm_scatter_t sc{};
     if (cg) {
       we.cgrad = cg;
       we.codec = m->codec;
       we.bfp_mode = m->bfp_mode;
+      if (m->fuse_scatter) {
+        // GEMM -> reduce-scatter: frame f of the bucket goes to rank f / shard, slot [rank][f % shard]
+        const int lo = blo[l];
+        uint8_t* inbox = m->layers[lo].cg[m->step_idx & 1];
+        const size_t frames = (bucket_count(lo, bhi[l]) + 511) / 512;
+        sc.nranks = nranks;
+        sc.rank = rank;
+        sc.shard_frames = (unsigned)((frames + nranks - 1) / nranks);
+        sc.frame0 = (unsigned)((L.g - m->layers[lo].g) / 512);
+        for (int r = 0; r < nranks; ++r) sc.inbox[r] = r == rank ? inbox : ainic_comm_peer_ptr(m->comm, inbox, r);
+        we.scatter = &sc;
+      }
     }
     TRY(ainic_gemm_bf16(AINIC_GEMM_TN, m->dact[l + 1], L.out, m->act[l], L.in, cg ? nullptr : L.g, L.in, L.out, L.in,
                         m->mb, &we, 0, m->wgrad_ctas, m->wgrad_stream));
@@ -344,16 +383,13 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
       TRY_CUDA(cudaEventRecord(L.dx_done, s));
     }
     // --- fused all-reduce + SGD on the comm stream, once the bucket that ends at layer l is full
-    pending_bytes += (size_t)L.in * L.out * 4;
-    if (l > 0 && pending_bytes < m->bucket_bytes) continue;
-    const int lo = l;                                   // bucket = layers lo .. hi, contiguous in the arenas
+    if (blo[l] != l) continue;
+    const int lo = l, hi = bhi[l];                      // bucket = layers lo .. hi, contiguous in the arenas
     TRY_CUDA(cudaStreamWaitEvent(m->comm_stream, L.dw_ready, 0));   // wgrad stream is in order: covers lo .. hi
     // the shadows of lo .. hi are rewritten below; the last backward-data GEMM that reads one of them
     // is layer max(lo,1)'s (main stream is in order)
     if (hi > 0) TRY_CUDA(cudaStreamWaitEvent(m->comm_stream, m->layers[lo > 0 ? lo : 1].dx_done, 0));
-    size_t count = 0;
-    for (int k = lo; k < hi; ++k) count += m->layers[k].slot;
-    count += (size_t)m->layers[hi].in * m->layers[hi].out;
+    const size_t count = bucket_count(lo, hi);
     ainic_allreduce_args_t a{};
     a.grad = L.g;
     a.weight = L.w;
@@ -365,11 +401,10 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
     a.algo = m->algo;
     a.max_ctas = m->comm_ctas;
     a.grad_compressed = cg;
+    a.grad_scattered = m->fuse_scatter ? 1 : 0;
     TRY(ainic_allreduce_fused(m->comm, &a, m->comm_stream));
     m->launches++;
     for (int k = lo; k <= hi; ++k) TRY_CUDA(cudaEventRecord(m->layers[k].updated, m->comm_stream));
-    hi = l - 1;
-    pending_bytes = 0;
   }
   m->first_step = false;
   m->step_idx++;

@@ -230,9 +230,10 @@ __device__ __forceinline__ void apply_full_w(const RankCtx& c, size_t f, const f
 // Reduce frames base + j, j = first, first + step, ... < lim over all ranks in rank order and hand
 // each sum to sink(j, acc, w) together with the frame's (already loaded) weights.  Peers are read in
 // batches of PB; batch k + 1 (possibly of the next frame) is requested before batch k is decoded.
-template <int CODEC, int MODE, class Sink>
-__device__ __forceinline__ void reduce_stream(const RankCtx& c, size_t parity_off, size_t base, size_t first, size_t step,
-                                              size_t lim, int lane, Sink sink) {
+// src(p, j) = where rank p's copy of frame base + j is read from.
+template <int CODEC, int MODE, class Src, class Sink>
+__device__ __forceinline__ void reduce_stream(const RankCtx& c, size_t base, size_t first, size_t step, size_t lim, int lane,
+                                              Src src, Sink sink) {
   using FC = FrameCodec<CODEC, MODE>;
   using Raw = typename FC::Raw;
   constexpr int PB = sizeof(Raw) > 32 ? 2 : 4;
@@ -244,7 +245,7 @@ __device__ __forceinline__ void reduce_stream(const RankCtx& c, size_t parity_of
   int b = 0;
 #pragma unroll
   for (int k = 0; k < PB; ++k)
-    if (k < N) FC::load(reduce_src<CODEC, MODE>(c, parity_off, k, base + j), cur[k], lane);
+    if (k < N) FC::load(src(k, j), cur[k], lane);
   float acc[16], w[16], v[16];
 #pragma unroll 1
   for (;;) {
@@ -255,7 +256,7 @@ __device__ __forceinline__ void reduce_stream(const RankCtx& c, size_t parity_of
     if (more) {
 #pragma unroll
       for (int k = 0; k < PB; ++k)
-        if (nbq * PB + k < N) FC::load(reduce_src<CODEC, MODE>(c, parity_off, nbq * PB + k, base + nj), nxt[k], lane);
+        if (nbq * PB + k < N) FC::load(src(nbq * PB + k, nj), nxt[k], lane);
     }
     if (b == 0 && c.weight) frame_load_f32(c.weight + (base + j) * kFrameVals, kFrameVals, w, lane);
 #pragma unroll
@@ -274,7 +275,8 @@ __device__ __forceinline__ void reduce_stream(const RankCtx& c, size_t parity_of
   }
 }
 
-// Two-shot gather: apply every other rank's published (reduced) shard.  A warp's (peer, frame) items
+// Two-shot gather: apply every other rank's published (reduced) shard (pulled over NVLink for fp32,
+// already pushed into local memory by its owner for the compressed codecs).  A warp's (peer, frame) items
 // form one flat sequence; they are fetched G at a time, group k + 1 while group k is applied, and
 // the weights of item i + 1 are requested before item i is decoded.
 template <int CODEC, int MODE>
@@ -300,7 +302,10 @@ __device__ __forceinline__ void gather_stream(const RankCtx& c, size_t shard, si
         const int p = (c.rank + dp) % N;
         const size_t f = (size_t)p * shard + j;
         fi[k] = (uint32_t)f;
-        FC::load(CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f * 2048 : c.stage_d[p] + j * FC::kBytes, r[k], lane);
+        // fp32: pull the reduced shard out of the owner's gradient buffer; compressed codecs: the owner
+        // already stored it into my stage D, slot [p][j]
+        FC::load(CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f * 2048
+                            : c.stage_d[c.rank] + ((size_t)p * shard + j) * FC::kBytes, r[k], lane);
         j += step;
         while (dp < N && j >= lim_of(dp)) { ++dp; j = first; }
       } else {
@@ -342,7 +347,7 @@ __device__ __noinline__ void tail_compress(const RankCtx& c, size_t parity_off, 
   FrameCodec<CODEC, MODE>::encode(a, c.stage_c[c.rank] + parity_off + f * FrameCodec<CODEC, MODE>::kBytes, lane);
 }
 // Reduce the partial frame over all ranks; publish it (two-shot: in place for fp32, re-encoded into
-// stage D slot j otherwise) when `publish`; apply it.
+// every other rank's stage D slot j otherwise) when `publish`; apply it.
 template <int CODEC, int MODE>
 __device__ __noinline__ void tail_reduce_apply(const RankCtx& c, size_t parity_off, size_t f, bool publish, size_t j, int lane) {
   using FC = FrameCodec<CODEC, MODE>;
@@ -353,10 +358,13 @@ __device__ __noinline__ void tail_reduce_apply(const RankCtx& c, size_t parity_o
     if (CODEC == 0) {
       if (c.nranks > 1) frame_store_f32(c.grad + f * kFrameVals, (int)(c.count - f * kFrameVals), acc, lane);
     } else {
-      uint8_t* dst = c.stage_d[c.rank] + j * FC::kBytes;
-      FC::encode(acc, dst, lane);
-      __syncwarp();
-      frame_decode<CODEC, MODE>(dst, acc, lane);
+      if constexpr (CODEC != 0) {   // push to every other rank's stage D, slot j = [my rank][index in shard]
+        typename FC::Raw q;
+        FC::pack(acc, q, lane);
+        for (int p = 0; p < c.nranks; ++p)
+          if (p != c.rank) FC::store(q, c.stage_d[p] + j * FC::kBytes, lane);
+        FC::unpack(q, acc, lane);
+      }
     }
   }
   apply_frame(c, f, acc, lane);
@@ -365,7 +373,7 @@ template <int CODEC, int MODE>
 __device__ __noinline__ void tail_gather_apply(const RankCtx& c, int p, size_t f, size_t j, int lane) {
   float g[16];
   if (CODEC == 0) frame_load_f32(c.peer_grad[p] + f * kFrameVals, (int)(c.count - f * kFrameVals), g, lane);
-  else frame_decode<CODEC, MODE>(c.stage_d[p] + j * FrameCodec<CODEC, MODE>::kBytes, g, lane);
+  else frame_decode<CODEC, MODE>(c.stage_d[c.rank] + j * FrameCodec<CODEC, MODE>::kBytes, g, lane);
   apply_frame(c, f, g, lane);
 }
 
@@ -391,7 +399,8 @@ __device__ void oneshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
     __syncthreads();
   }
   mark_phase(ws, 0);
-  reduce_stream<CODEC, MODE>(c, parity_off, 0, first, step, full, lane,
+  reduce_stream<CODEC, MODE>(c, 0, first, step, full, lane,
+                             [&](int p, size_t f) { return reduce_src<CODEC, MODE>(c, parity_off, p, f); },
                              [&](size_t f, float (&acc)[16], float (&w)[16]) { apply_full_w(c, f, acc, w, lane); });
   if (own_tail) tail_reduce_apply<CODEC, MODE>(c, parity_off, full, false, 0, lane);
   if (CODEC == 0 && N > 1) {  // peers read my gradient in place: do not return before they are done
@@ -441,17 +450,29 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   // phase 1: reduce my shard from every rank, publish it re-encoded, update my shard's weights
   {
     const size_t base = (size_t)c.rank * shard, lim = shard_full(c.rank);
-    reduce_stream<CODEC, MODE>(c, parity_off, base, first, step, lim, lane, [&](size_t j, float (&acc)[16], float (&w)[16]) {
-      if (CODEC == 0) {
+    // scattered input (precompressed == 2): every rank's GEMM epilogue already stored its copy of my
+    // shard into my inbox, slot [p][j] - the reduce phase touches local memory only
+    const bool inbox = CODEC != 0 && c.precompressed == 2;
+    auto src = [&](int p, size_t j) -> const uint8_t* {
+      return inbox ? c.stage_c[c.rank] + ((size_t)p * shard + j) * FC::kBytes : reduce_src<CODEC, MODE>(c, parity_off, p, base + j);
+    };
+    reduce_stream<CODEC, MODE>(c, base, first, step, lim, lane, src, [&](size_t j, float (&acc)[16], float (&w)[16]) {
+      if constexpr (CODEC == 0) {
         // in place: peers pull the reduced shard out of my gradient buffer
         if (N > 1) frame_store_f32(c.grad + (base + j) * kFrameVals, kFrameVals, acc, lane);
       } else {
-        // publish, then apply exactly what the peers will decode (fixes SURVEY D11)
-        frame_encode_rt<CODEC, MODE>(acc, c.stage_d[c.rank] + j * FC::kBytes, lane);
+        // publish: quantise once, store the frame into EVERY rank's stage D at slot [my rank][j]
+        // (NVLink stores, nothing waits for them until the flag below), then apply exactly what the
+        // peers will decode (fixes SURVEY D11)
+        typename FC::Raw q;
+        FC::pack(acc, q, lane);
+        const size_t slot = ((size_t)c.rank * shard + j) * FC::kBytes;
+        for (int dp = 1; dp < N; ++dp) FC::store(q, c.stage_d[(c.rank + dp) % N] + slot, lane);
+        FC::unpack(q, acc, lane);
       }
       apply_full_w(c, base + j, acc, w, lane);
     });
-    if (own_tail && ts == c.rank) tail_reduce_apply<CODEC, MODE>(c, parity_off, full, true, tj, lane);
+    if (own_tail && ts == c.rank) tail_reduce_apply<CODEC, MODE>(c, parity_off, full, true, (size_t)c.rank * shard + tj, lane);
   }
   if (N == 1) return;
   signal_all(c, 1, cta, c.epoch);
@@ -459,7 +480,7 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   mark_phase(ws, 1);
   // phase 2: pull every other rank's reduced shard
   gather_stream<CODEC, MODE>(c, shard, full, first, step, lane);
-  if (own_tail && ts != c.rank) tail_gather_apply<CODEC, MODE>(c, ts, full, tj, lane);
+  if (own_tail && ts != c.rank) tail_gather_apply<CODEC, MODE>(c, ts, full, (size_t)ts * shard + tj, lane);
   if (CODEC == 0) {
     signal_all(c, 2, cta, c.epoch);
     wait_all(c, 2, cta, c.epoch, ws);

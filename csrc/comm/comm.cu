@@ -253,7 +253,8 @@ extern "C" int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args
   if (!c->connected) { set_error("communicator not connected"); return AINIC_ERR_ARG; }
   if (((uintptr_t)a->grad & 15) || ((uintptr_t)a->weight & 15) || ((uintptr_t)a->weight_bf16 & 7) || ((uintptr_t)a->grad_out & 15))
     return AINIC_ERR_ARG;
-  const int algo = resolve_algo(a->algo, c->nranks, a->count);
+  const bool scattered = a->grad_scattered && a->grad_compressed && a->codec != AINIC_CODEC_F32;
+  const int algo = scattered ? AINIC_ALGO_TWOSHOT : resolve_algo(a->algo, c->nranks, a->count);
   KernFn kern = pick_kernel(algo, a->codec, a->bfp_mode);
   if (!kern) { set_error("unsupported algo/codec combination"); return AINIC_ERR_UNSUPPORTED; }
   if (c->nranks > 1 && !ainic_comm_peer_ptr(c, a->grad, 0) && a->codec == AINIC_CODEC_F32) {
@@ -320,6 +321,11 @@ extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_a
     ctx.parity = 0;
     ctx.stage_c_half = 0;
     ctx.precompressed = 1;
+    if (a->grad_scattered) {
+      // every rank's GEMM epilogue stored its frames of my shard into this buffer already
+      if (a->count % kFrameVals) { set_error("scattered gradients need count % 512 == 0"); return AINIC_ERR_ARG; }
+      ctx.precompressed = 2;
+    }
   }
   return AINIC_OK;
 }

@@ -86,6 +86,31 @@ struct FrameCodec<1, MODE> {
     }
     frame[kBfpExpOff + lane] = (uint8_t)e_lane;
   }
+  // encode into registers (same bytes encode() writes) / store such a frame; used to publish one
+  // reduced frame to several ranks without quantising it more than once
+  __device__ static __forceinline__ void pack(const float (&v)[16], Raw& r, int lane) {
+    uint32_t e_lane = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t E = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) E = max(E, bfp_exp_field(__float_as_uint(v[4 * i + j])));
+      E = max(E, __shfl_xor_sync(kFullMask, E, 1));
+      E = max(E, __shfl_xor_sync(kFullMask, E, 2));
+      uint32_t word = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) word |= ((uint32_t)bfp_quant(v[4 * i + j], E, MODE) & 0xFFu) << (8 * j);
+      r.w[i] = word;
+      const uint32_t t = __shfl_sync(kFullMask, E, (lane & 7) * 4);
+      if ((lane >> 3) == i) e_lane = t;
+    }
+    r.e = e_lane;
+  }
+  __device__ static __forceinline__ void store(const Raw& r, uint8_t* frame, int lane) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) *reinterpret_cast<uint32_t*>(frame + i * 128 + lane * 4) = r.w[i];
+    frame[kBfpExpOff + lane] = (uint8_t)r.e;
+  }
   // encode + replace v by what a reader of the frame will decode (no trip through memory)
   __device__ static __forceinline__ void encode_rt(float (&v)[16], uint8_t* frame, int lane) {
     uint32_t e_lane = 0;
@@ -151,6 +176,32 @@ struct FrameCodec<2, MODE> {
     }
     if (lane < 16) frame[kMxScaleOff + lane] = (uint8_t)s_lane;
   }
+  __device__ static __forceinline__ void pack(const float (&v)[16], Raw& r, int lane) {
+    uint32_t s_lane = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t E = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) E = max(E, bfp_exp_field(__float_as_uint(v[4 * i + j])));
+      E = max(E, __shfl_xor_sync(kFullMask, E, 1));
+      E = max(E, __shfl_xor_sync(kFullMask, E, 2));
+      E = max(E, __shfl_xor_sync(kFullMask, E, 4));
+      const uint32_t sb = mx_scale_byte(E);
+      const float inv = mx_inv_scale(sb);
+      uint32_t word = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) word |= f32_to_e4m3(v[4 * i + j] * inv) << (8 * j);
+      r.w[i] = word;
+      const uint32_t t = __shfl_sync(kFullMask, sb, (lane & 3) * 8);
+      if ((lane >> 2) == i) s_lane = t;
+    }
+    r.s = __shfl_sync(kFullMask, s_lane, lane & 15);   // same lane -> byte mapping as load()
+  }
+  __device__ static __forceinline__ void store(const Raw& r, uint8_t* frame, int lane) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) *reinterpret_cast<uint32_t*>(frame + i * 128 + lane * 4) = r.w[i];
+    if (lane < 16) frame[kMxScaleOff + lane] = (uint8_t)r.s;
+  }
 };
 
 // ---------------------------------------------------------------- bf16
@@ -173,6 +224,18 @@ struct FrameCodec<3, MODE> {
       v[4 * i + 2] = __uint_as_float(r.q[i].y << 16);
       v[4 * i + 3] = __uint_as_float(r.q[i].y & 0xFFFF0000u);
     }
+  }
+  __device__ static __forceinline__ void pack(const float (&v)[16], Raw& r, int lane) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      __nv_bfloat162 a = __floats2bfloat162_rn(v[4 * i], v[4 * i + 1]);
+      __nv_bfloat162 b = __floats2bfloat162_rn(v[4 * i + 2], v[4 * i + 3]);
+      r.q[i] = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+    }
+  }
+  __device__ static __forceinline__ void store(const Raw& r, uint8_t* frame, int lane) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) *reinterpret_cast<uint2*>(frame + i * 256 + lane * 8) = r.q[i];
   }
   __device__ static __forceinline__ void encode(const float (&v)[16], uint8_t* frame, int lane) {
 #pragma unroll

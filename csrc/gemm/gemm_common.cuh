@@ -38,6 +38,10 @@ struct EpiParams {
   uint8_t* cgrad;          // compressed output (OUT_COMPRESSED): frames of the flat [M][ldc] bucket
   int codec, bfp_mode;     // AINIC_CODEC_BFP / AINIC_CODEC_MXFP8, AINIC_BFP_*
   int epi_sleep;           // ns the epilogue warps sleep between polls of the accumulator barrier (0 = spin)
+  // reduce-scatter in the epilogue (ainic_gemm_scatter_t): frame f -> inbox of rank f / shard
+  uint8_t* push[AINIC_MAX_RANKS];
+  int push_n, push_rank;   // push_n <= 1: frames go to cgrad
+  uint32_t push_shard, push_frame0;
 };
 
 // Output selector of the epilogue.
@@ -51,8 +55,16 @@ constexpr int OUT_BF16 = 0, OUT_FP32 = 1, OUT_COMPRESSED = 2;
 __device__ __forceinline__ void store_compressed32(const EpiParams& ep, size_t idx, const float (&v)[32]) {
   const size_t frame = idx >> 9;
   const uint32_t off = (uint32_t)(idx & 511);
+  const size_t fbytes = ep.codec == AINIC_CODEC_BFP ? (size_t)kBfpFrameBytes : (size_t)kMxFrameBytes;
+  uint8_t* fr;
+  if (ep.push_n > 1) {  // the frame's owner reduces it: store it there (NVLink store, fire and forget)
+    const uint32_t F = ep.push_frame0 + (uint32_t)frame;
+    const uint32_t owner = F / ep.push_shard;
+    fr = ep.push[owner] + ((size_t)ep.push_rank * ep.push_shard + (F - owner * ep.push_shard)) * fbytes;
+  } else {
+    fr = ep.cgrad + frame * fbytes;
+  }
   if (ep.codec == AINIC_CODEC_BFP) {
-    uint8_t* fr = ep.cgrad + frame * kBfpFrameBytes;
     uint32_t exps = 0;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -67,7 +79,6 @@ __device__ __forceinline__ void store_compressed32(const EpiParams& ep, size_t i
     }
     *reinterpret_cast<uint16_t*>(fr + kBfpExpOff + (off >> 4)) = (uint16_t)exps;
   } else {  // MXFP8
-    uint8_t* fr = ep.cgrad + frame * kMxFrameBytes;
     uint32_t E = 0;
 #pragma unroll
     for (int j = 0; j < 32; ++j) E = max(E, bfp_exp_field(__float_as_uint(v[j])));

@@ -245,6 +245,22 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
     ep.cgrad = static_cast<uint8_t*>(epi->cgrad);
     ep.codec = epi->codec;
     ep.bfp_mode = epi->bfp_mode;
+    if (const ainic_gemm_scatter_t* sc = epi->scatter) {
+      if (sc->nranks < 1 || sc->nranks > AINIC_MAX_RANKS || sc->rank < 0 || sc->rank >= sc->nranks || sc->shard_frames == 0)
+        return AINIC_ERR_ARG;
+      const size_t frames = ((size_t)M * ldc + 511) / 512;
+      if (((size_t)sc->frame0 + frames + sc->shard_frames - 1) / sc->shard_frames > (size_t)sc->nranks) return AINIC_ERR_ARG;
+      for (int r = 0; r < sc->nranks; ++r) {
+        if (!sc->inbox[r] || ((uintptr_t)sc->inbox[r] & 15)) return AINIC_ERR_ARG;
+        ep.push[r] = static_cast<uint8_t*>(sc->inbox[r]);
+      }
+      ep.push_n = sc->nranks;
+      ep.push_rank = sc->rank;
+      ep.push_shard = sc->shard_frames;
+      ep.push_frame0 = sc->frame0;
+      ep.cgrad = ep.push[sc->rank];   // selects the compressed epilogue
+      if (sc->nranks == 1) { ep.cgrad += (size_t)sc->frame0 * (ep.codec == AINIC_CODEC_BFP ? 544 : 528); }
+    }
   }
   if (ep.cgrad) {  // compressed gradient output: backward-weight layout only, whole 32-value groups
     if (layout != AINIC_GEMM_TN || (N % 32) || (ldc % 32) || ((uintptr_t)ep.cgrad & 15) ||

@@ -28,15 +28,21 @@ class NativeError(RuntimeError):
 ERRORS = {0: "ok", -1: "bad argument", -2: "CUDA error", -3: "timeout", -4: "busy", -5: "aborted", -6: "unsupported"}
 
 
+class GemmScatter(C.Structure):
+    _fields_ = [("inbox", vp * 8), ("nranks", C.c_int), ("rank", C.c_int), ("shard_frames", C.c_uint),
+                ("frame0", C.c_uint)]
+
+
 class GemmEpilogue(C.Structure):
     _fields_ = [("bias", vp), ("mask_out", vp), ("mask_in", vp), ("alpha", C.c_float), ("relu", C.c_int),
-                ("accumulate", C.c_int), ("cgrad", vp), ("codec", C.c_int), ("bfp_mode", C.c_int)]
+                ("accumulate", C.c_int), ("cgrad", vp), ("codec", C.c_int), ("bfp_mode", C.c_int),
+                ("scatter", C.POINTER(GemmScatter))]
 
 
 class AllreduceArgs(C.Structure):
     _fields_ = [("grad", vp), ("weight", vp), ("weight_bf16", vp), ("grad_out", vp), ("count", sz), ("lr", C.c_float),
                 ("codec", C.c_int), ("bfp_mode", C.c_int), ("algo", C.c_int), ("max_ctas", C.c_int),
-                ("grad_compressed", vp)]
+                ("grad_compressed", vp), ("grad_scattered", C.c_int)]
 
 
 class Rqst(C.Structure):

@@ -62,9 +62,8 @@ class MLPConfig:
     def heap_bytes(self, world: int = 8) -> int:
         p = self.param_count() + 1024 * self.nlayers
         biggest = max(self.sizes[l] * self.sizes[l + 1] for l in range(self.nlayers))
-        # a bucket closes once it holds >= bucket_mb, so it is smaller than bucket_mb + the biggest layer;
-        # sized for the default AND an explicit setting because the staging area only grows
-        bucket = int(max(self.resolved_bucket_mb(world), 80.0 if world >= 8 else 0.0) * (1 << 20) / 4)
+        # a bucket closes once it holds >= bucket_mb, so it is smaller than bucket_mb + the biggest layer
+        bucket = int(self.resolved_bucket_mb(world) * (1 << 20) / 4)
         frames = (min(p, bucket + biggest) + 1023) // 512 + (biggest + 511) // 512
         # fp32 weights + fp32 gradients, two compressed-gradient buffers per layer (GEMM epilogue output),
         # the communicator's staging for the largest bucket, slack for alignment
@@ -88,11 +87,21 @@ class MLPTrainer:
         self.algo = K.ALGO_NAMES[cfg.algo]
         sizes = (C.c_int * len(cfg.sizes))(*cfg.sizes)
         h = C.c_void_p()
-        N.check(self.lib.ainic_mlp_create(C.byref(h), self.comm.handle, cfg.nlayers, sizes, cfg.mb, cfg.fuse, cfg.lr,
-                                          cfg.loss_weight, self.codec, cfg.bfp_mode, self.algo), "mlp_create")
-        self.handle = h
+        # the bucket size is read at create time (AINIC_BUCKET_MB) so that the communicator's staging is
+        # sized once; a later set_bucket_mb() may grow it, which abandons the old area inside the heap
+        saved = os.environ.get("AINIC_BUCKET_MB")
         if cfg.bucket_mb is not None:
-            self.set_bucket_mb(cfg.bucket_mb)
+            os.environ["AINIC_BUCKET_MB"] = repr(float(cfg.bucket_mb))
+        try:
+            N.check(self.lib.ainic_mlp_create(C.byref(h), self.comm.handle, cfg.nlayers, sizes, cfg.mb, cfg.fuse, cfg.lr,
+                                              cfg.loss_weight, self.codec, cfg.bfp_mode, self.algo), "mlp_create")
+        finally:
+            if cfg.bucket_mb is not None:
+                if saved is None:
+                    os.environ.pop("AINIC_BUCKET_MB", None)
+                else:
+                    os.environ["AINIC_BUCKET_MB"] = saved
+        self.handle = h
         self.device = self.comm.device
         self.loss_dev = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._views: dict = {}

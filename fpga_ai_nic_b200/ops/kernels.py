@@ -147,17 +147,34 @@ def gemm_bwd_data(dy: torch.Tensor, w: torch.Tensor, mask_in: torch.Tensor | Non
 
 def gemm_bwd_weight(dy: torch.Tensor, x: torch.Tensor, out: torch.Tensor | None = None, accumulate: bool = False,
                     alpha: float = 1.0, block_n: int = 0, max_ctas: int = 0, stream=None,
-                    compressed_out: torch.Tensor | None = None, codec: int = CODEC_BFP, bfp_mode: int = CLEAN) -> torch.Tensor:
+                    compressed_out: torch.Tensor | None = None, codec: int = CODEC_BFP, bfp_mode: int = CLEAN,
+                    scatter: tuple | None = None) -> torch.Tensor:
     """dw[n,k] = dy[mb,n]^T @ x[mb,k] as fp32, written straight into the flat gradient bucket.
 
     With ``compressed_out`` (uint8, ``bfp_bytes(n*k)`` / ``mx_bytes(n*k)``) the epilogue instead emits the
     gradient already in BFP / MXFP8 frame layout - what ``Communicator.allreduce_fused(grad_compressed=...)``
-    consumes - and no fp32 gradient is written."""
+    consumes - and no fp32 gradient is written.
+
+    ``scatter=(inboxes, rank, shard_frames, frame0)`` turns the epilogue into a reduce-scatter: frame f of
+    the bucket (this GEMM's frames start at ``frame0``) is stored into ``inboxes[f // shard_frames]`` at slot
+    ``[rank][f % shard_frames]`` (ainic_gemm_scatter_t).  ``inboxes`` are uint8 tensors or raw pointers."""
     _chk(dy, torch.bfloat16)
     _chk(x, torch.bfloat16)
     mb, n = dy.shape
     k = x.shape[1]
     assert x.shape[0] == mb
+    if scatter is not None:
+        inboxes, rank, shard_frames, frame0 = scatter
+        sc = N.GemmScatter()
+        for i, t in enumerate(inboxes):
+            sc.inbox[i] = t.data_ptr() if isinstance(t, torch.Tensor) else int(t)
+        sc.nranks, sc.rank, sc.shard_frames, sc.frame0 = len(inboxes), rank, shard_frames, frame0
+        epi = N.GemmEpilogue(None, None, None, alpha, 0, 0, None, codec, bfp_mode, C.pointer(sc))
+        rc = N.cuda().ainic_gemm_bf16(GEMM_TN, dy.data_ptr(), dy.stride(0), x.data_ptr(), x.stride(0), None, k, n, k, mb,
+                                      C.byref(epi), block_n, max_ctas, N.stream_ptr(stream))
+        N.check(rc, "gemm_bf16(scatter)")
+        _count()
+        return None
     if compressed_out is not None:
         _chk(compressed_out, torch.uint8)
         epi = N.GemmEpilogue(None, None, None, alpha, 0, 0, compressed_out.data_ptr(), codec, bfp_mode)

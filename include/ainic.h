@@ -62,6 +62,20 @@ int ainic_cast_f32_bf16(const float* x, void* y_bf16, size_t count, void* stream
 #define AINIC_GEMM_NT 0 /* C[M,N] = A[M,K] . B[N,K]^T  bf16 out  (forward)        */
 #define AINIC_GEMM_NN 1 /* C[M,N] = A[M,K] . B[K,N]    bf16 out  (backward data)  */
 #define AINIC_GEMM_TN 2 /* C[M,N] = A[K,M]^T . B[K,N]  fp32 out  (backward weight)*/
+/* GEMM -> reduce-scatter in one kernel: the backward-weight epilogue stores every compressed frame
+ * straight into the memory of the rank that will reduce it (plain stores on peer-mapped pointers,
+ * tile by tile while the tensor cores work on the next tile).  A bucket of F frames is cut into
+ * nranks shards of shard_frames = ceil(F / nranks); frame f belongs to rank f / shard_frames and
+ * lands in that rank's inbox at slot [rank][f % shard_frames] (row pitch shard_frames frames).
+ * No counterpart in the reference, whose NIC DMA-reads the finished fp32 buffer
+ * (hw/all_reduce.sv:246-532); it is what sitting the codec and the wire behind the adder tree
+ * becomes when the "adder tree" is a tensor-core GEMM. */
+typedef struct ainic_gemm_scatter {
+  void* inbox[AINIC_MAX_RANKS]; /* inbox base of every rank as mapped into this process ([rank] is local) */
+  int nranks, rank;
+  unsigned shard_frames;        /* frames per owner */
+  unsigned frame0;              /* index of this GEMM's first frame inside the bucket */
+} ainic_gemm_scatter_t;
 typedef struct ainic_gemm_epilogue {
   const float* bias;      /* [N], added before activation (bf16 outputs) */
   uint8_t* mask_out;      /* [M][ldc] ReLU mask written by the forward pass */
@@ -74,6 +88,7 @@ typedef struct ainic_gemm_epilogue {
                              args.grad_compressed is set); needs N % 32 == 0 and ldc % 32 == 0 */
   int codec;              /* AINIC_CODEC_BFP or AINIC_CODEC_MXFP8 when cgrad is set */
   int bfp_mode;
+  const ainic_gemm_scatter_t* scatter; /* nullable; with it cgrad is ignored and the frames go to the owners' inboxes */
 } ainic_gemm_epilogue_t;
 /* bf16 operands, fp32 accumulation on tcgen05 tensor cores.  block_n = 0 picks the tile width,
  * max_ctas = 0 uses every SM (a smaller value leaves SMs for a concurrent all-reduce kernel). */
@@ -121,6 +136,9 @@ typedef struct ainic_allreduce_args {
                             heap (written by the GEMM epilogue); the kernel then skips its compression pass and
                             `grad` is only used for its size.  The caller alternates between two such buffers
                             from call to call on the same bucket. */
+  int grad_scattered; /* nonzero: grad_compressed is this rank's INBOX, already filled by every rank's GEMM
+                         epilogue (ainic_gemm_scatter_t layout, shard_frames = ceil(frames / nranks)): the
+                         reduce phase reads local memory only.  Two-shot only; algo is ignored. */
 } ainic_allreduce_args_t;
 /* Fused compress -> (peer pull) -> fp32 reduce -> decompress -> SGD, one kernel launch on stream. */
 int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args_t* args, void* stream);

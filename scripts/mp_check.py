@@ -238,28 +238,36 @@ for codec in ("f32", "bfp"):
         update_rel_err_vs_oracle=rel, timeouts=comm.counters()["timeouts"])
     if not ok:
         fails.append(("mlp", codec))
-    w_final = [tr.buffer("weight", l).cpu().clone() for l in range(cfg.nlayers)]
     tr.close()
-    # 3b. gradient bucketing: several layers per fused call (and the compressed GEMM epilogue) must
-    # give the same bits as one call per layer - the sum order and the codec blocks do not depend on
-    # which rank owns a frame.
-    variants = [(1000.0, None), (0.6, None)] + ([(1000.0, "1"), (0.0, "1")] if codec == "bfp" and world > 1 else [])
-    for bucket_mb, fusec in variants:
-        if fusec is not None:
-            os.environ["AINIC_FUSE_COMPRESS"] = fusec
-        tb = MLPTrainer(MLPConfig(**{**cfg.__dict__, "bucket_mb": bucket_mb}), comm=comm)
+    # 3b. gradient bucketing, the compressed GEMM epilogue (1) and the GEMM -> reduce-scatter epilogue (2)
+    # must give the same bits as one call per layer on fp32 gradients: the sum order and the codec
+    # blocks do not depend on which rank owns a frame or on who compressed it.  The algorithm is pinned
+    # (auto would pick one-shot for small buckets and two-shot for large ones, which round differently).
+    algo = "twoshot" if world > 1 else "auto"
+
+    def run_variant(bucket_mb, fusec):
+        os.environ["AINIC_FUSE_COMPRESS"] = fusec
+        tb = MLPTrainer(MLPConfig(**{**cfg.__dict__, "bucket_mb": bucket_mb, "algo": algo}), comm=comm)
         os.environ.pop("AINIC_FUSE_COMPRESS", None)
         for _ in range(steps):
             tb.step(xb, yd)
         tb.wait()
         torch.cuda.synchronize()
-        same = all(torch.equal(tb.buffer("weight", l).cpu(), w_final[l]) for l in range(cfg.nlayers))
-        same = all_ok(same)
+        out = [tb.buffer("weight", l).cpu().clone() for l in range(cfg.nlayers)]
+        tb.close()
+        return out
+
+    base = run_variant(0.0, "0")
+    variants = [(1000.0, "0"), (0.6, "0")]
+    if codec == "bfp" and world > 1:
+        variants += [(0.0, "1"), (1000.0, "1"), (0.0, "2"), (0.6, "2"), (1000.0, "2")]
+    for bucket_mb, fusec in variants:
+        got = run_variant(bucket_mb, fusec)
+        same = all_ok(all(torch.equal(got[l], base[l]) for l in range(cfg.nlayers)))
         say(check="mlp_bucketed", codec=codec, bucket_mb=bucket_mb, fuse_compress=fusec, ok=same,
             timeouts=comm.counters()["timeouts"])
         if not same:
             fails.append(("mlp_bucketed", codec, bucket_mb, fusec))
-        tb.close()
 
 if world > 1:
     dist.barrier()

@@ -126,6 +126,36 @@ def test_gemm_bwd_weight_compressed_epilogue(K, codec, mode, mb, n, k, block_n):
     assert torch.equal(got, want)
 
 
+@pytest.mark.parametrize("codec", ["bfp", "mxfp8"])
+@pytest.mark.parametrize("nranks,rank,frame0,extra", [(4, 2, 5, 3), (8, 7, 0, 0), (2, 0, 130, 1), (1, 0, 4, 0)])
+def test_gemm_scatter_epilogue(K, codec, nranks, rank, frame0, extra):
+    """GEMM -> reduce-scatter: every frame lands in its owner's inbox at slot [rank][frame % shard]
+    (ainic_gemm_scatter_t); here the "peers" are nranks buffers on one GPU."""
+    torch.manual_seed(8)
+    mb, n, k = 256, 256, 512
+    dy = (torch.randn(mb, n, device="cuda") * 0.05).bfloat16()
+    x = (torch.randn(mb, k, device="cuda") * 0.5).bfloat16()
+    frames = n * k // 512
+    fb = 544 if codec == "bfp" else 528
+    code = K.CODEC_BFP if codec == "bfp" else K.CODEC_MXFP8
+    want = torch.zeros(frames * fb, dtype=torch.uint8, device="cuda")
+    K.gemm_bwd_weight(dy, x, compressed_out=want, codec=code)
+    total = frame0 + frames + extra                       # frames of the whole bucket
+    shard = (total + nranks - 1) // nranks
+    inbox = [torch.full((nranks * shard * fb,), 0xEE, dtype=torch.uint8, device="cuda") for _ in range(nranks)]
+    K.gemm_bwd_weight(dy, x, codec=code, scatter=(inbox, rank, shard, frame0))
+    torch.cuda.synchronize()
+    want = want.view(frames, fb).cpu()
+    got = [b.view(nranks, shard, fb).cpu() for b in inbox]
+    touched = 0
+    for f in range(frames):
+        o, j = divmod(frame0 + f, shard)
+        assert torch.equal(got[o][rank, j], want[f]), (f, o, j)
+        touched += 1
+    # nothing else was written
+    assert sum(int((g != 0xEE).any(dim=-1).sum()) for g in got) <= touched
+
+
 def test_gemm_fused_epilogues(K):
     torch.manual_seed(3)
     mb, n, k = 256, 512, 384
