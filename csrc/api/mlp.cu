@@ -72,6 +72,18 @@ struct ainic_mlp {
   __nv_bfloat16* wb_arena = nullptr;
   uint8_t* cg_arena[2] = {nullptr, nullptr};
   size_t bucket_bytes = 0;
+  // CUDA-graph replay of the whole iteration (one launch per step instead of ~30 kernel launches and
+  // ~100 event operations).  One instantiated graph per (input, labels, loss, parity) tuple.
+  struct StepGraph {
+    const void* x; const int32_t* labels; float* loss_out; unsigned parity; size_t bucket_bytes;
+    cudaGraphExec_t exec; unsigned long long kernels;
+  };
+  std::vector<StepGraph> graphs;
+  bool use_graph = false;
+  bool in_capture = false;
+  bool events_stale = false;         // the per-layer events were last recorded inside a capture
+  cudaEvent_t step_done = nullptr;   // end of the last graph-replayed step on the caller's stream
+  cudaStream_t cap_stream = nullptr; // origin stream of captures (the caller's may be the legacy stream, which cannot capture)
 };
 
 static size_t max_bucket_count(const ainic_mlp* m);
@@ -116,6 +128,11 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
     m->fuse_compress = mode >= 1 && n > 1 && (codec == AINIC_CODEC_BFP || codec == AINIC_CODEC_MXFP8);
     // AINIC_FUSE_COMPRESS=2: the epilogue also performs the reduce-scatter's data movement - each frame
     // is stored into the inbox of the rank that owns it, over NVLink, while the GEMM is still running.
+    // Bit-identical results (scripts/mp_check.py 3b), but measured SLOWER: 1.39 vs 0.80 ms/step at 8
+    // ranks, 0.81 vs 0.71 at 2.  A thread of the epilogue owns 32 values of one row (tcgen05.ld
+    // 32x32b), so a warp's stores are 32 separate 16-byte pieces of 32 different frames; over NVLink
+    // those are tiny write packets and the epilogue stalls on them.  Opt-in until the tile is
+    // transposed through shared memory into whole 544-byte frames.
     m->fuse_scatter = m->fuse_compress && mode == 2;
   }
   m->layers.resize(nlayers);
@@ -167,13 +184,20 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
     }
   }
   {
-    // default bucket size: per layer up to 4 ranks; from 8 ranks the all-reduce queue is the critical
-    // path and its fixed cost per call (three cross-GPU flag exchanges) dominates 16 MiB buckets.
+    // default bucket size: 80 MiB as soon as there is a peer.  Each fused call pays three cross-GPU flag
+    // exchanges plus the launch skew between ranks whatever its size; measured on the reference MLP
+    // (ms/step, per-layer -> 80 MiB): 0.767 -> 0.700 at 2 ranks, 0.959 -> 0.784 at 8 ranks.
     const int n = ainic_comm_size(comm);
-    m->bucket_bytes = n >= 8 ? (size_t)80 << 20 : 0;
+    m->bucket_bytes = n >= 2 ? (size_t)80 << 20 : 0;
     if (const char* e = getenv("AINIC_BUCKET_MB")) m->bucket_bytes = (size_t)(atof(e) * 1048576.0);
   }
   TRY(ainic_comm_reserve(comm, max_bucket_count(m)));
+  // Graph replay is on by default on one rank.  With peers the fused all-reduce takes a per-call epoch
+  // as a kernel argument (the cross-GPU flag value), which a replayed launch cannot advance.
+  m->use_graph = ainic_comm_size(comm) == 1;
+  if (const char* e = getenv("AINIC_MLP_GRAPH")) m->use_graph = atoi(e) != 0 && ainic_comm_size(comm) == 1;
+  TRY_CUDA(cudaEventCreateWithFlags(&m->step_done, cudaEventDisableTiming));
+  TRY_CUDA(cudaStreamCreateWithFlags(&m->cap_stream, cudaStreamNonBlocking));
   size_t off = 0;
   for (int l = 0; l < nlayers; ++l) {
     Layer& L = m->layers[l];
@@ -210,6 +234,9 @@ extern "C" int ainic_mlp_destroy(ainic_mlp_t* m) {
   for (auto p : m->dact) cudaFree(p);
   cudaFree(m->loss_sum);
   cudaEventDestroy(m->fwd_done);
+  cudaEventDestroy(m->step_done);
+  cudaStreamDestroy(m->cap_stream);
+  for (auto& g : m->graphs) cudaGraphExecDestroy(g.exec);
   cudaStreamDestroy(m->wgrad_stream);
   cudaStreamDestroy(m->comm_stream);
   delete m;
@@ -271,7 +298,7 @@ static int forward(ainic_mlp* m, cudaStream_t s, bool wait_updates) {
   const bool use_bias = (m->fuse == 1 || m->fuse == 3), relu = (m->fuse >= 2);
   for (int l = 0; l < m->nlayers; ++l) {
     Layer& L = m->layers[l];
-    if (wait_updates && !m->first_step) TRY_CUDA(cudaStreamWaitEvent(s, L.updated, 0));
+    if (wait_updates && !m->first_step && !m->events_stale) TRY_CUDA(cudaStreamWaitEvent(s, L.updated, 0));
     ainic_gemm_epilogue_t epi{};
     epi.bias = use_bias ? L.bias : nullptr;
     epi.relu = relu ? 1 : 0;
@@ -288,6 +315,7 @@ static int forward(ainic_mlp* m, cudaStream_t s, bool wait_updates) {
 extern "C" int ainic_mlp_forward(ainic_mlp_t* m, const void* x_bf16, void* stream) {
   if (!m || !x_bf16) return AINIC_ERR_ARG;
   cudaStream_t s = (cudaStream_t)stream;
+  if (m->events_stale) TRY_CUDA(cudaStreamWaitEvent(s, m->step_done, 0));
   if (x_bf16 != m->act[0])
     TRY_CUDA(cudaMemcpyAsync(m->act[0], x_bf16, (size_t)m->mb * m->layers[0].in * 2, cudaMemcpyDeviceToDevice, s));
   return forward(m, s, true);
@@ -295,11 +323,15 @@ extern "C" int ainic_mlp_forward(ainic_mlp_t* m, const void* x_bf16, void* strea
 
 // One full training iteration.  loss_out (device, nullable) receives the mean cross-entropy of this
 // rank's minibatch.  Returns after enqueueing; completion is stream/event ordered.
-extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t* labels, float* loss_out, void* stream) {
-  if (!m || !x_bf16 || !labels) return AINIC_ERR_ARG;
-  cudaStream_t s = (cudaStream_t)stream;
+static int step_body(ainic_mlp* m, const void* x_bf16, const int32_t* labels, float* loss_out, cudaStream_t s) {
   const int Ln = m->nlayers;
   const bool relu = (m->fuse >= 2), use_bias = (m->fuse == 1 || m->fuse == 3);
+  if (m->events_stale && !m->in_capture) {
+    // the previous step was a graph replay on some stream: order after it, then behave like a first step
+    TRY_CUDA(cudaStreamWaitEvent(s, m->step_done, 0));
+    m->first_step = true;
+    m->events_stale = false;
+  }
   // act[0] is still being read by the previous step's last weight-gradient GEMM (wgrad stream is
   // in order, so layer 0's event covers all of them).
   if (!m->first_step) TRY_CUDA(cudaStreamWaitEvent(s, m->layers[0].dw_ready, 0));
@@ -406,6 +438,12 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
     m->launches++;
     for (int k = lo; k <= hi; ++k) TRY_CUDA(cudaEventRecord(m->layers[k].updated, m->comm_stream));
   }
+  if (m->in_capture) {
+    // join the forked streams: the graph ends when the last update has landed (every weight-gradient
+    // GEMM precedes a dw_ready that some bucket's all-reduce waited for)
+    for (auto& L : m->layers) TRY_CUDA(cudaStreamWaitEvent(s, L.updated, 0));
+    return AINIC_OK;
+  }
   m->first_step = false;
   m->step_idx++;
   if (m->profile) {
@@ -421,6 +459,66 @@ extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t*
     }
     m->prof_steps++;
   }
+  return AINIC_OK;
+}
+
+// One full training iteration (public entry).  On one rank the iteration is captured into a CUDA graph
+// the first time a given (input, labels, loss) tuple is seen and replayed afterwards: the streams,
+// events and kernels of step_body become graph nodes and edges, and a step costs one launch.  The
+// graph of step i + 1 starts when step i's last update has landed - no overlap is lost, because the
+// first thing a step needs (layer 0's weights) is the last thing the previous step produces.
+extern "C" int ainic_mlp_step(ainic_mlp_t* m, const void* x_bf16, const int32_t* labels, float* loss_out, void* stream) {
+  if (!m || !x_bf16 || !labels) return AINIC_ERR_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!m->use_graph || m->profile) return step_body(m, x_bf16, labels, loss_out, s);
+  const unsigned parity = (unsigned)(m->step_idx & 1);
+  ainic_mlp::StepGraph* g = nullptr;
+  for (auto& e : m->graphs)
+    if (e.x == x_bf16 && e.labels == labels && e.loss_out == loss_out && e.parity == parity && e.bucket_bytes == m->bucket_bytes) g = &e;
+  if (!g) {
+    if (m->graphs.size() >= 32) {  // callers that never reuse their buffers get no benefit: start over
+      for (auto& e : m->graphs) cudaGraphExecDestroy(e.exec);
+      m->graphs.clear();
+    }
+    if (!m->first_step && !m->events_stale) {  // a direct step is still in flight on other streams
+      for (auto& L : m->layers) TRY_CUDA(cudaStreamWaitEvent(s, L.updated, 0));
+    }
+    const unsigned long long before = m->launches;
+    const bool was_first = m->first_step;
+    cudaGraph_t graph = nullptr;
+    TRY_CUDA(cudaStreamBeginCapture(m->cap_stream, cudaStreamCaptureModeThreadLocal));
+    m->in_capture = true;
+    m->first_step = true;            // no waits on events recorded outside the capture
+    const int rc = step_body(m, x_bf16, labels, loss_out, m->cap_stream);
+    m->in_capture = false;
+    m->first_step = was_first;
+    const cudaError_t ce = cudaStreamEndCapture(m->cap_stream, &graph);
+    const unsigned long long kernels = m->launches - before;
+    m->launches = before;
+    if (rc || ce != cudaSuccess || !graph) {
+      if (graph) cudaGraphDestroy(graph);
+      cudaGetLastError();
+      fprintf(stderr, "ainic_mlp: graph capture failed (%s); falling back to direct launches\n", cudaGetErrorString(ce));
+      m->use_graph = false;
+      return step_body(m, x_bf16, labels, loss_out, s);
+    }
+    cudaGraphExec_t exec = nullptr;
+    const cudaError_t ie = cudaGraphInstantiate(&exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ie != cudaSuccess) {
+      cudaGetLastError();
+      m->use_graph = false;
+      return step_body(m, x_bf16, labels, loss_out, s);
+    }
+    m->graphs.push_back({x_bf16, labels, loss_out, parity, m->bucket_bytes, exec, kernels});
+    g = &m->graphs.back();
+  }
+  TRY_CUDA(cudaGraphLaunch(g->exec, s));
+  TRY_CUDA(cudaEventRecord(m->step_done, s));
+  m->launches += g->kernels;
+  m->events_stale = true;
+  m->first_step = false;
+  m->step_idx++;
   return AINIC_OK;
 }
 
@@ -445,6 +543,10 @@ extern "C" unsigned long long ainic_mlp_profile(ainic_mlp_t* m, int enable, doub
 extern "C" int ainic_mlp_wait_updates(ainic_mlp_t* m, void* stream) {
   if (!m) return AINIC_ERR_ARG;
   if (m->first_step) return AINIC_OK;
+  if (m->events_stale) {
+    TRY_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, m->step_done, 0));
+    return AINIC_OK;
+  }
   for (auto& L : m->layers) TRY_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, L.updated, 0));
   return AINIC_OK;
 }

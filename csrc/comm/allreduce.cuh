@@ -275,8 +275,7 @@ __device__ __forceinline__ void reduce_stream(const RankCtx& c, size_t base, siz
   }
 }
 
-// Two-shot gather: apply every other rank's published (reduced) shard (pulled over NVLink for fp32,
-// already pushed into local memory by its owner for the compressed codecs).  A warp's (peer, frame) items
+// Two-shot gather: apply every other rank's published (reduced) shard.  A warp's (peer, frame) items
 // form one flat sequence; they are fetched G at a time, group k + 1 while group k is applied, and
 // the weights of item i + 1 are requested before item i is decoded.
 template <int CODEC, int MODE>
@@ -302,10 +301,7 @@ __device__ __forceinline__ void gather_stream(const RankCtx& c, size_t shard, si
         const int p = (c.rank + dp) % N;
         const size_t f = (size_t)p * shard + j;
         fi[k] = (uint32_t)f;
-        // fp32: pull the reduced shard out of the owner's gradient buffer; compressed codecs: the owner
-        // already stored it into my stage D, slot [p][j]
-        FC::load(CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f * 2048
-                            : c.stage_d[c.rank] + ((size_t)p * shard + j) * FC::kBytes, r[k], lane);
+        FC::load(CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f * 2048 : c.stage_d[p] + j * FC::kBytes, r[k], lane);
         j += step;
         while (dp < N && j >= lim_of(dp)) { ++dp; j = first; }
       } else {
@@ -347,7 +343,7 @@ __device__ __noinline__ void tail_compress(const RankCtx& c, size_t parity_off, 
   FrameCodec<CODEC, MODE>::encode(a, c.stage_c[c.rank] + parity_off + f * FrameCodec<CODEC, MODE>::kBytes, lane);
 }
 // Reduce the partial frame over all ranks; publish it (two-shot: in place for fp32, re-encoded into
-// every other rank's stage D slot j otherwise) when `publish`; apply it.
+// stage D slot j otherwise) when `publish`; apply it.
 template <int CODEC, int MODE>
 __device__ __noinline__ void tail_reduce_apply(const RankCtx& c, size_t parity_off, size_t f, bool publish, size_t j, int lane) {
   using FC = FrameCodec<CODEC, MODE>;
@@ -358,13 +354,10 @@ __device__ __noinline__ void tail_reduce_apply(const RankCtx& c, size_t parity_o
     if (CODEC == 0) {
       if (c.nranks > 1) frame_store_f32(c.grad + f * kFrameVals, (int)(c.count - f * kFrameVals), acc, lane);
     } else {
-      if constexpr (CODEC != 0) {   // push to every other rank's stage D, slot j = [my rank][index in shard]
-        typename FC::Raw q;
-        FC::pack(acc, q, lane);
-        for (int p = 0; p < c.nranks; ++p)
-          if (p != c.rank) FC::store(q, c.stage_d[p] + j * FC::kBytes, lane);
-        FC::unpack(q, acc, lane);
-      }
+      uint8_t* dst = c.stage_d[c.rank] + j * FC::kBytes;
+      FC::encode(acc, dst, lane);
+      __syncwarp();
+      frame_decode<CODEC, MODE>(dst, acc, lane);
     }
   }
   apply_frame(c, f, acc, lane);
@@ -373,7 +366,7 @@ template <int CODEC, int MODE>
 __device__ __noinline__ void tail_gather_apply(const RankCtx& c, int p, size_t f, size_t j, int lane) {
   float g[16];
   if (CODEC == 0) frame_load_f32(c.peer_grad[p] + f * kFrameVals, (int)(c.count - f * kFrameVals), g, lane);
-  else frame_decode<CODEC, MODE>(c.stage_d[c.rank] + j * FrameCodec<CODEC, MODE>::kBytes, g, lane);
+  else frame_decode<CODEC, MODE>(c.stage_d[p] + j * FrameCodec<CODEC, MODE>::kBytes, g, lane);
   apply_frame(c, f, g, lane);
 }
 
@@ -461,18 +454,15 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
         // in place: peers pull the reduced shard out of my gradient buffer
         if (N > 1) frame_store_f32(c.grad + (base + j) * kFrameVals, kFrameVals, acc, lane);
       } else {
-        // publish: quantise once, store the frame into EVERY rank's stage D at slot [my rank][j]
-        // (NVLink stores, nothing waits for them until the flag below), then apply exactly what the
-        // peers will decode (fixes SURVEY D11)
-        typename FC::Raw q;
-        FC::pack(acc, q, lane);
-        const size_t slot = ((size_t)c.rank * shard + j) * FC::kBytes;
-        for (int dp = 1; dp < N; ++dp) FC::store(q, c.stage_d[(c.rank + dp) % N] + slot, lane);
-        FC::unpack(q, acc, lane);
+        // publish into my stage D (the peers pull it in phase 2), then apply exactly what they will
+        // decode (fixes SURVEY D11).  Pushing the frame into every peer's stage D instead was measured
+        // at 8 ranks: the gather phase shrinks (57 -> 39 us on an 80 MiB bucket) but the reduce phase
+        // grows by more (66 -> 98 us); see profiles/README.md section 3.
+        frame_encode_rt<CODEC, MODE>(acc, c.stage_d[c.rank] + j * FC::kBytes, lane);
       }
       apply_full_w(c, base + j, acc, w, lane);
     });
-    if (own_tail && ts == c.rank) tail_reduce_apply<CODEC, MODE>(c, parity_off, full, true, (size_t)c.rank * shard + tj, lane);
+    if (own_tail && ts == c.rank) tail_reduce_apply<CODEC, MODE>(c, parity_off, full, true, tj, lane);
   }
   if (N == 1) return;
   signal_all(c, 1, cta, c.epoch);
@@ -480,7 +470,7 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   mark_phase(ws, 1);
   // phase 2: pull every other rank's reduced shard
   gather_stream<CODEC, MODE>(c, shard, full, first, step, lane);
-  if (own_tail && ts != c.rank) tail_gather_apply<CODEC, MODE>(c, ts, full, (size_t)ts * shard + tj, lane);
+  if (own_tail && ts != c.rank) tail_gather_apply<CODEC, MODE>(c, ts, full, tj, lane);
   if (CODEC == 0) {
     signal_all(c, 2, cta, c.epoch);
     wait_all(c, 2, cta, c.epoch, ws);

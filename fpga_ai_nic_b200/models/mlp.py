@@ -32,7 +32,7 @@ class MLPConfig:
     seed: int = 1                                              # libxsmm_rng_set_seed(1), :273
     init_scale: float = 1.0                                    # multiplies the reference init (wide layers need < 1)
     bucket_mb: float | None = None                             # fp32 MiB of gradients per all-reduce call; 0 = per
-                                                               # layer (reference, :754); None = 80 from 8 ranks, else 0
+                                                               # layer (reference, :754); None = 80 from 2 ranks, else 0
 
     @staticmethod
     def reference(nlayers: int = 10, width: int = 2048, mb: int = 1792) -> "MLPConfig":
@@ -57,7 +57,7 @@ class MLPConfig:
             return float(self.bucket_mb)
         if os.environ.get("AINIC_BUCKET_MB"):
             return float(os.environ["AINIC_BUCKET_MB"])
-        return 80.0 if world >= 8 else 0.0
+        return 80.0 if world >= 2 else 0.0
 
     def heap_bytes(self, world: int = 8) -> int:
         p = self.param_count() + 1024 * self.nlayers
@@ -150,14 +150,17 @@ class MLPTrainer:
         N.check(self.lib.ainic_mlp_forward(self.handle, x.data_ptr(), N.stream_ptr()), "mlp_forward")
         return self.buffer("act", self.cfg.nlayers)
 
-    def step(self, x: torch.Tensor, labels: torch.Tensor, want_loss: bool = True) -> torch.Tensor | None:
+    def step(self, x: torch.Tensor, labels: torch.Tensor, want_loss: bool = True,
+             loss_out: torch.Tensor | None = None) -> torch.Tensor | None:
         """One training iteration (enqueue only).  Returns the device scalar holding this rank's
-        summed cross-entropy (divide by mb for the mean)."""
+        summed cross-entropy (divide by mb for the mean); ``loss_out`` (fp32[1], device) replaces the
+        trainer's own scalar, e.g. to keep several steps' losses in flight."""
         assert x.dtype == torch.bfloat16 and x.is_cuda and x.is_contiguous()
         assert labels.dtype == torch.int32 and labels.is_cuda
+        dst = loss_out if loss_out is not None else self.loss_dev
         N.check(self.lib.ainic_mlp_step(self.handle, x.data_ptr(), labels.data_ptr(),
-                                        self.loss_dev.data_ptr() if want_loss else None, N.stream_ptr()), "mlp_step")
-        return self.loss_dev if want_loss else None
+                                        dst.data_ptr() if want_loss else None, N.stream_ptr()), "mlp_step")
+        return dst if want_loss else None
 
     def set_bucket_mb(self, mb: float) -> None:
         """Gradient bucket size (fp32 MiB collected from the last layer down before one fused

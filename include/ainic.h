@@ -213,8 +213,8 @@ unsigned long long ainic_mlp_profile(ainic_mlp_t* m, int enable, double out_ms[4
 unsigned long long ainic_mlp_launches(ainic_mlp_t* m);
 /* Gradient bucketing: consecutive layers are contiguous in memory, so one fused all-reduce can cover
  * several.  bytes = fp32 gradient bytes to collect (from the last layer down) before a call is
- * issued; 0 = one call per layer like the reference (sw/mlp_mpi_example_f32.cpp:754).  Default: 0 up
- * to 4 ranks, 80 MiB from 8 ranks; AINIC_BUCKET_MB overrides at create time. */
+ * issued; 0 = one call per layer like the reference (sw/mlp_mpi_example_f32.cpp:754).  Default: 0 on
+ * one rank, 80 MiB from 2 ranks; AINIC_BUCKET_MB overrides at create time. */
 int ainic_mlp_set_bucket_bytes(ainic_mlp_t* m, size_t bytes);
 size_t ainic_mlp_bucket_bytes(ainic_mlp_t* m);
 void* ainic_mlp_loss_ptr(ainic_mlp_t* m);

@@ -152,3 +152,38 @@ def test_bucketed_allreduce_same_bits_as_per_layer(bucket_mb):
     assert out[0][1] == 12 and out[1][1] == (3 if bucket_mb > 100 else 6)
     for a, b in zip(out[0][0], out[1][0]):
         assert torch.equal(a, b)
+
+
+def test_graph_replay_same_bits_as_direct_launches(monkeypatch):
+    """On one rank the step is captured into a CUDA graph per (input, labels, loss) tuple and replayed;
+    results, launch counts and mixing with direct steps (profile mode) must not change anything."""
+    from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer
+    from fpga_ai_nic_b200.ops import kernels as K
+    cfg = MLPConfig(sizes=[256, 384, 256, 128], mb=256, fuse=3, lr=0.5, loss_weight=1.0)
+    g = torch.Generator().manual_seed(21)
+    xs = [K.cast_bf16((torch.rand(cfg.mb, 256, generator=g) - 0.5).cuda()) for _ in range(2)]
+    ys = [torch.randint(0, 128, (cfg.mb,), generator=g, dtype=torch.int32).cuda() for _ in range(2)]
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("AINIC_MLP_GRAPH", mode)
+        tr = MLPTrainer(cfg)
+        l0 = tr.launches
+        losses = []
+        for i in range(6):
+            if mode == "1" and i == 3:
+                tr.profile(True)              # profile mode runs direct launches in between replays
+            tr.step(xs[i % 2], ys[i % 2])
+            if mode == "1" and i == 3:
+                assert tr.profile(False)["steps"] == 1
+            losses.append(tr.loss_dev.clone())
+        tr.wait()
+        torch.cuda.synchronize()
+        out[mode] = ([tr.buffer("weight", l).cpu().clone() for l in range(cfg.nlayers)], [float(v) for v in losses],
+                     tr.launches - l0)
+        assert tr.check_health()["timeouts"] == 0
+        tr.close()
+    assert out["0"][2] == out["1"][2] > 0
+    # the loss is an atomicAdd reduction over rows (order varies run to run); the weights do not depend on it
+    assert out["0"][1] == pytest.approx(out["1"][1], rel=1e-5)
+    for a, b in zip(out["0"][0], out["1"][0]):
+        assert torch.equal(a, b)
