@@ -192,10 +192,11 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
     if (const char* e = getenv("AINIC_BUCKET_MB")) m->bucket_bytes = (size_t)(atof(e) * 1048576.0);
   }
   TRY(ainic_comm_reserve(comm, max_bucket_count(m)));
-  // Graph replay is on by default on one rank.  With peers the fused all-reduce takes a per-call epoch
-  // as a kernel argument (the cross-GPU flag value), which a replayed launch cannot advance.
-  m->use_graph = ainic_comm_size(comm) == 1;
-  if (const char* e = getenv("AINIC_MLP_GRAPH")) m->use_graph = atoi(e) != 0 && ainic_comm_size(comm) == 1;
+  // Graph replay is on by default (AINIC_MLP_GRAPH=0 switches it off).  It needs launch arguments that do
+  // not change from step to step: the fused all-reduce keeps its call number (the cross-GPU flag value)
+  // in device memory for that reason, and the compressed-gradient double buffer is part of the graph key.
+  m->use_graph = true;
+  if (const char* e = getenv("AINIC_MLP_GRAPH")) m->use_graph = atoi(e) != 0;
   TRY_CUDA(cudaEventCreateWithFlags(&m->step_done, cudaEventDisableTiming));
   TRY_CUDA(cudaStreamCreateWithFlags(&m->cap_stream, cudaStreamNonBlocking));
   size_t off = 0;
@@ -462,8 +463,8 @@ static int step_body(ainic_mlp* m, const void* x_bf16, const int32_t* labels, fl
   return AINIC_OK;
 }
 
-// One full training iteration (public entry).  On one rank the iteration is captured into a CUDA graph
-// the first time a given (input, labels, loss) tuple is seen and replayed afterwards: the streams,
+// One full training iteration (public entry).  The iteration is captured into a CUDA graph the first
+// time a given (input, labels, loss) tuple is seen and replayed afterwards: the streams,
 // events and kernels of step_body become graph nodes and edges, and a step costs one launch.  The
 // graph of step i + 1 starts when step i's last update has landed - no overlap is lost, because the
 // first thing a step needs (layer 0's weights) is the last thing the previous step produces.

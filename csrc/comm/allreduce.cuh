@@ -56,6 +56,9 @@ struct RankCtx {
   float lr;
   uint32_t epoch;                // increments on every fused call (all ranks issue the same sequence)
   uint32_t parity;               // which half of stage_c this call writes (toggles per staging call)
+  uint32_t* epoch_ptr;           // non-null: the call number lives in device memory (this call is *epoch_ptr + 1,
+                                 // parity = its low bit; the last CTA stores it back).  Launch arguments are then
+                                 // the same for every call, so a captured launch can be replayed (CUDA graphs).
   uint32_t precompressed;        // stage_c already holds this rank's encoded gradient (GEMM epilogue wrote it)
   unsigned long long timeout_ns;
 };
@@ -80,10 +83,36 @@ __device__ __forceinline__ bool spin_until(const uint32_t* f, uint32_t target, u
 }
 
 struct WaitStats {
+  uint32_t epoch, parity;      // this call's number / staging half (from the arguments or from device memory)
   unsigned long long wait_ns;
   unsigned long long mark[2];  // %globaltimer after the first / second cross-rank barrier (CTA 0 reports them)
   uint32_t timeouts;
 };
+// Thread 0, before the first __syncthreads of the kernel.
+__device__ __forceinline__ void begin_call(const RankCtx& c, WaitStats& ws) {
+  ws.wait_ns = 0; ws.timeouts = 0; ws.mark[0] = 0; ws.mark[1] = 0;
+  if (c.epoch_ptr) {
+    ws.epoch = *reinterpret_cast<volatile uint32_t*>(c.epoch_ptr) + 1u;
+    ws.parity = ws.epoch & 1u;
+  } else {
+    ws.epoch = c.epoch;
+    ws.parity = c.parity;
+  }
+}
+// Thread 0 of every CTA, after its work is done: the last CTA to arrive publishes the call number for
+// the next launch (every CTA of this launch has read it long before) and raises the done word.
+__device__ __forceinline__ void end_call(const RankCtx& c, const WaitStats& ws, int nctas) {
+  __threadfence_system();
+  const unsigned long long ticket = atomicAdd(c.counters + CTR_TICKET, 1ull);
+  if (ticket == (unsigned long long)(nctas - 1)) {
+    c.counters[CTR_TICKET] = 0;
+    if (c.epoch_ptr) *reinterpret_cast<volatile uint32_t*>(c.epoch_ptr) = ws.epoch;
+    if (c.done_slot) {
+      __threadfence_system();
+      *c.done_slot = 1u;  // 512'd1 into the request's done cache line (hw/all_reduce.sv:1368-1375)
+    }
+  }
+}
 __device__ __forceinline__ void mark_phase(WaitStats& ws, int i) {
   if (threadIdx.x == 0) ws.mark[i] = ptx::globaltimer_ns();
 }
@@ -377,7 +406,7 @@ __device__ void oneshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   const size_t frames = bfp_frames(c.count);
   const size_t full = c.count / kFrameVals;                       // frames [0, full) are complete
   const int N = c.nranks;
-  const size_t parity_off = c.parity ? c.stage_c_half : 0;
+  const size_t parity_off = ws.parity ? c.stage_c_half : 0;
   const size_t first = (size_t)cta + (size_t)warp * nctas, step = (size_t)nctas * wpb;
   const bool own_tail = full < frames && (int)(full % nctas) == cta && (int)((full / nctas) % wpb) == warp;
   if (CODEC != 0 && !c.precompressed) {
@@ -386,8 +415,8 @@ __device__ void oneshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
     if (own_tail) tail_compress<CODEC, MODE>(c, parity_off, full, lane);
   }
   if (N > 1) {
-    signal_all(c, 0, cta, c.epoch);
-    wait_all(c, 0, cta, c.epoch, ws);
+    signal_all(c, 0, cta, ws.epoch);
+    wait_all(c, 0, cta, ws.epoch, ws);
   } else {
     __syncthreads();
   }
@@ -397,8 +426,8 @@ __device__ void oneshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
                              [&](size_t f, float (&acc)[16], float (&w)[16]) { apply_full_w(c, f, acc, w, lane); });
   if (own_tail) tail_reduce_apply<CODEC, MODE>(c, parity_off, full, false, 0, lane);
   if (CODEC == 0 && N > 1) {  // peers read my gradient in place: do not return before they are done
-    signal_all(c, 2, cta, c.epoch);
-    wait_all(c, 2, cta, c.epoch, ws);
+    signal_all(c, 2, cta, ws.epoch);
+    wait_all(c, 2, cta, ws.epoch, ws);
   }
 }
 
@@ -411,7 +440,7 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   const size_t full = c.count / kFrameVals;
   const int N = c.nranks;
   const size_t shard = (frames + N - 1) / N;  // frames per shard
-  const size_t parity_off = c.parity ? c.stage_c_half : 0;
+  const size_t parity_off = ws.parity ? c.stage_c_half : 0;
   const size_t first = (size_t)cta + (size_t)warp * nctas, step = (size_t)nctas * wpb;
   // the partial frame (if any): shard ts, index tj inside it; CTA b handles the same j of every shard,
   // so that a peer's CTA b finds exactly the frames it needs behind CTA b's flag
@@ -434,8 +463,8 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
     if (own_tail) tail_compress<CODEC, MODE>(c, parity_off, full, lane);
   }
   if (N > 1) {
-    signal_all(c, 0, cta, c.epoch);
-    wait_all(c, 0, cta, c.epoch, ws);
+    signal_all(c, 0, cta, ws.epoch);
+    wait_all(c, 0, cta, ws.epoch, ws);
   } else {
     __syncthreads();
   }
@@ -465,15 +494,15 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
     if (own_tail && ts == c.rank) tail_reduce_apply<CODEC, MODE>(c, parity_off, full, true, tj, lane);
   }
   if (N == 1) return;
-  signal_all(c, 1, cta, c.epoch);
-  wait_all(c, 1, cta, c.epoch, ws);
+  signal_all(c, 1, cta, ws.epoch);
+  wait_all(c, 1, cta, ws.epoch, ws);
   mark_phase(ws, 1);
   // phase 2: pull every other rank's reduced shard
   gather_stream<CODEC, MODE>(c, shard, full, first, step, lane);
   if (own_tail && ts != c.rank) tail_gather_apply<CODEC, MODE>(c, ts, full, tj, lane);
   if (CODEC == 0) {
-    signal_all(c, 2, cta, c.epoch);
-    wait_all(c, 2, cta, c.epoch, ws);
+    signal_all(c, 2, cta, ws.epoch);
+    wait_all(c, 2, cta, ws.epoch, ws);
   }
 }
 
@@ -503,10 +532,10 @@ __device__ void ring_body(const RankCtx& c, int cta, int nctas, WaitStats& ws) {
   // My inbox is written by `up`; `down`'s inbox is written by me.  The start barrier guarantees
   // every rank has finished its previous fused call (stream order), i.e. all inboxes are drained -
   // the role the read credits play in the reference (hw/all_reduce.sv:468-483).
-  signal_all(c, 0, cta, c.epoch);
-  wait_all(c, 0, cta, c.epoch, ws);
+  signal_all(c, 0, cta, ws.epoch);
+  wait_all(c, 0, cta, ws.epoch, ws);
   uint32_t sent = 0, recvd = 0;
-  const uint32_t seq_base = c.epoch << 12;
+  const uint32_t seq_base = ws.epoch << 12;
   for (size_t blk = cta; blk < nblocks; blk += nctas) {
     uint8_t* outbox = c.stage_d[down] + blk * msgs_per_block * slot_bytes;
     const uint8_t* inbox = c.stage_d[n] + blk * msgs_per_block * slot_bytes;
@@ -554,7 +583,7 @@ __device__ void ring_body(const RankCtx& c, int cta, int nctas, WaitStats& ws) {
 template <int ALGO, int CODEC, int MODE>
 __device__ __forceinline__ void run_rank(const RankCtx& c, int cta, int nctas) {
   __shared__ WaitStats ws;
-  if (threadIdx.x == 0) { ws.wait_ns = 0; ws.timeouts = 0; ws.mark[0] = 0; ws.mark[1] = 0; }
+  if (threadIdx.x == 0) begin_call(c, ws);
   const unsigned long long t0 = ptx::globaltimer_ns();
   __syncthreads();
   if (ALGO == AINIC_ALGO_ONESHOT) oneshot_body<CODEC, MODE>(c, cta, nctas, ws);
@@ -572,15 +601,7 @@ __device__ __forceinline__ void run_rank(const RankCtx& c, int cta, int nctas) {
       if (ws.mark[0]) atomicAdd(c.counters + CTR_TO_BARRIER0_NS, ws.mark[0] - t0);
       if (ws.mark[1]) atomicAdd(c.counters + CTR_TO_BARRIER1_NS, ws.mark[1] - t0);
     }
-    __threadfence_system();
-    const unsigned long long ticket = atomicAdd(c.counters + CTR_TICKET, 1ull);
-    if (ticket == (unsigned long long)(nctas - 1)) {
-      c.counters[CTR_TICKET] = 0;
-      if (c.done_slot) {
-        __threadfence_system();
-        *c.done_slot = 1u;  // 512'd1 into the request's done cache line (hw/all_reduce.sv:1368-1375)
-      }
-    }
+    end_call(c, ws, nctas);
   }
 }
 

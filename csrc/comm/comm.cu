@@ -41,7 +41,7 @@ struct ainic_comm {
   uint8_t* stage_c = nullptr;             // in heap, 2 halves
   uint8_t* stage_d = nullptr;             // in heap
   size_t stage_frames = 0;
-  uint32_t epoch = 0, parity = 0;
+  uint32_t* epoch_dev = nullptr;   // device word: number of completed fused calls
   unsigned long long timeout_ns = 10ull * 1000 * 1000 * 1000;
   volatile uint32_t* next_done_slot = nullptr;  // set by the NIC layer for the next launch
 };
@@ -65,6 +65,7 @@ extern "C" int ainic_comm_create(ainic_comm_t** out, int rank, int nranks, size_
   cudaDeviceSynchronize();
   c->flags = reinterpret_cast<uint32_t*>(c->heap);
   c->counters = reinterpret_cast<unsigned long long*>(c->heap + align_up(kFlagWords * sizeof(uint32_t), 4096));
+  c->epoch_dev = reinterpret_cast<uint32_t*>(c->counters + 32);   // same zeroed page, past the counters
   c->bump = reserved;
   c->peer_base[rank] = c->heap;
   c->connected = (nranks == 1);
@@ -305,8 +306,10 @@ extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_a
   ctx.count = a->count;
   ctx.stage_c_half = c->stage_frames * 1024;
   ctx.lr = a->lr;
-  ctx.epoch = ++c->epoch;
-  ctx.parity = (c->parity ^= 1u);
+  // the call number lives in device memory (epoch_dev): identical launch arguments from call to call
+  ctx.epoch = 0;
+  ctx.parity = 0;
+  ctx.epoch_ptr = c->epoch_dev;
   ctx.timeout_ns = c->timeout_ns;
   ctx.precompressed = 0;
   if (a->grad_compressed && a->codec != AINIC_CODEC_F32) {

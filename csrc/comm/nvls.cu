@@ -313,7 +313,7 @@ __device__ __forceinline__ void fence_alias() { asm volatile("fence.proxy.alias;
 __global__ void __launch_bounds__(kCommThreads) allreduce_nvls_kernel(const NvlsCtx x) {
   const RankCtx& c = x.base;
   __shared__ WaitStats ws;
-  if (threadIdx.x == 0) { ws.wait_ns = 0; ws.timeouts = 0; }
+  if (threadIdx.x == 0) begin_call(c, ws);
   const unsigned long long t0 = ptx::globaltimer_ns();
   __syncthreads();
   const int cta = blockIdx.x, nctas = gridDim.x;
@@ -321,8 +321,8 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_nvls_kernel(const Nvls
   const int N = c.nranks;
   const size_t frames = c.count / kFrameVals;       // whole frames only (host enforces count % 512 == 0)
   const size_t shard = (frames + N - 1) / N;
-  signal_all(c, 0, cta, c.epoch);
-  wait_all(c, 0, cta, c.epoch, ws);
+  signal_all(c, 0, cta, ws.epoch);
+  wait_all(c, 0, cta, ws.epoch, ws);
   fence_alias();
   float v[16];
   for (size_t j = (size_t)cta + (size_t)warp * nctas; j < shard; j += (size_t)nctas * wpb) {
@@ -342,8 +342,8 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_nvls_kernel(const Nvls
     apply_frame(c, f, v, lane);
   }
   fence_alias();
-  signal_all(c, 1, cta, c.epoch);
-  wait_all(c, 1, cta, c.epoch, ws);
+  signal_all(c, 1, cta, ws.epoch);
+  wait_all(c, 1, cta, ws.epoch, ws);
   fence_alias();
   for (int dp = 1; dp < N; ++dp) {
     const int p = (c.rank + dp) % N;
@@ -364,6 +364,7 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_nvls_kernel(const Nvls
       atomicAdd(c.counters + CTR_LAUNCHES, 1ull);
       c.counters[CTR_LAST_NS] = t1 - t0;
     }
+    end_call(c, ws, nctas);
   }
 }
 
