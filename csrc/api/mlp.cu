@@ -113,17 +113,15 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
   if (const char* e = getenv("AINIC_COMM_CTAS")) m->comm_ctas = atoi(e);
   if (const char* e = getenv("AINIC_GEMM_CTAS")) m->gemm_ctas = atoi(e);
   if (const char* e = getenv("AINIC_WGRAD_CTAS")) m->wgrad_ctas = atoi(e);
-  // With more than one rank and a block-compressed wire format the weight-gradient GEMM writes the
-  // wire format itself (the reference's BFP adapter sits right behind the adder tree the same way,
-  // hw/all_reduce.sv:745-772): no fp32 gradient in memory, no compression pass in the all-reduce.
-  // It takes 10-20 us off every all-reduce call but the quantisation lengthens the GEMM's exposed
-  // epilogue.  Measured on the reference MLP: at 2 ranks it costs more than it saves (0.80 vs 0.77
-  // ms/step), at 8 ranks - where the all-reduce queue, not the GEMM chain, is the critical path - it
-  // wins (1.04 vs 1.16 ms/step); 4 ranks are a wash (0.95 vs 0.94).  Default: on from 8 ranks;
-  // AINIC_FUSE_COMPRESS=0/1 overrides.
+  // With a block-compressed wire format the weight-gradient GEMM can write the wire format itself (the
+  // reference's BFP adapter sits right behind the adder tree the same way, hw/all_reduce.sv:745-772):
+  // no fp32 gradient in memory, no compression pass in the all-reduce.  The all-reduce gets shorter,
+  // the GEMM's exposed epilogue longer.  Measured on the reference MLP with 80 MiB buckets (ms/step,
+  // off -> on): 2 ranks 0.703 -> 0.710, 4 ranks 0.698 -> 0.657, 8 ranks 0.844 -> 0.800.  Default: on
+  // from 4 ranks; AINIC_FUSE_COMPRESS=0/1/2 overrides.
   {
     const int n = ainic_comm_size(comm);
-    int mode = n >= 8 ? 1 : 0;
+    int mode = n >= 4 ? 1 : 0;
     if (const char* e = getenv("AINIC_FUSE_COMPRESS")) mode = atoi(e);
     m->fuse_compress = mode >= 1 && n > 1 && (codec == AINIC_CODEC_BFP || codec == AINIC_CODEC_MXFP8);
     // AINIC_FUSE_COMPRESS=2: the epilogue also performs the reduce-scatter's data movement - each frame
