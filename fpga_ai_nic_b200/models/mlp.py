@@ -140,6 +140,36 @@ class MLPTrainer:
             self.buffer("bias", l).copy_(O.init_buf(self.cfg.sizes[l + 1], seed=self.cfg.seed * 1000 + 500 + l))
         self.sync_shadows()
 
+    def broadcast_parameters(self, src: int = 0) -> None:
+        """Rank ``src``'s weights and biases replace everyone's - the reference's MPI_Bcast of
+        fil_libxsmm / bias_libxsmm after rank 0 initialised them (sw/mlp_mpi_example_f32.cpp:463-470).
+        Start-up plumbing, so it goes through torch.distributed; the shadows are rebuilt afterwards."""
+        import torch.distributed as dist
+        if self.world > 1:
+            for l in range(self.cfg.nlayers):
+                dist.broadcast(self.buffer("weight", l), src=src)
+                dist.broadcast(self.buffer("bias", l), src=src)
+        self.sync_shadows()
+
+    def scatter_batch(self, x: torch.Tensor | None, y: torch.Tensor | None, src: int = 0):
+        """Split a global minibatch held by rank ``src`` ([world*mb, C0] fp32/bf16 and [world*mb] int32) into
+        per-rank shards, like the reference's MPI_Scatter of the activations (:453-460).  Returns this
+        rank's (x bf16 [mb, C0], y int32 [mb]) on the trainer's device."""
+        import torch.distributed as dist
+        mb, c0 = self.cfg.mb, self.cfg.sizes[0]
+        xs = torch.empty(mb, c0, dtype=torch.bfloat16, device=self.device)
+        ys = torch.empty(mb, dtype=torch.int32, device=self.device)
+        if self.world == 1:
+            xs.copy_(x.to(self.device).reshape(mb, c0))
+            ys.copy_(y.to(self.device))
+            return xs, ys
+        is_src = self.comm.rank == src
+        xl = list(x.to(self.device).bfloat16().reshape(self.world, mb, c0).unbind(0)) if is_src else None
+        yl = list(y.to(self.device).to(torch.int32).reshape(self.world, mb).unbind(0)) if is_src else None
+        dist.scatter(xs, xl, src=src)
+        dist.scatter(ys, yl, src=src)
+        return xs, ys
+
     def sync_shadows(self) -> None:
         N.check(self.lib.ainic_mlp_sync_shadows(self.handle, N.stream_ptr()), "mlp_sync_shadows")
         torch.cuda.current_stream().synchronize()

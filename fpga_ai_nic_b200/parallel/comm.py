@@ -82,11 +82,16 @@ class Communicator:
     def allreduce_fused(self, grad: torch.Tensor, weight: torch.Tensor | None = None, lr: float = 0.0,
                         weight_bf16: torch.Tensor | None = None, grad_out: torch.Tensor | None = None,
                         codec: int = K.CODEC_BFP, bfp_mode: int = K.CLEAN, algo: int = K.ALGO_AUTO, max_ctas: int = 0,
-                        stream=None, grad_compressed: torch.Tensor | None = None) -> None:
+                        stream=None, grad_compressed: torch.Tensor | None = None, grad_scattered: bool = False) -> None:
+        """One fused launch: compress -> peer exchange -> fp32 reduce in rank order -> decompress -> SGD.
+        ``grad_compressed``: this rank's gradient already as frames inside the symmetric heap (GEMM
+        epilogue output); with ``grad_scattered`` it is this rank's inbox filled by every rank's
+        GEMM -> reduce-scatter epilogue (ainic_gemm_scatter_t layout)."""
         a = N.AllreduceArgs(grad.data_ptr(), weight.data_ptr() if weight is not None else None,
                             weight_bf16.data_ptr() if weight_bf16 is not None else None,
                             grad_out.data_ptr() if grad_out is not None else None, grad.numel(), lr, codec, bfp_mode,
-                            algo, max_ctas, grad_compressed.data_ptr() if grad_compressed is not None else None)
+                            algo, max_ctas, grad_compressed.data_ptr() if grad_compressed is not None else None,
+                            1 if grad_scattered else 0)
         N.check(self.lib.ainic_allreduce_fused(self.handle, C.byref(a), N.stream_ptr(stream)), "allreduce_fused")
         K._count()
 

@@ -7,7 +7,11 @@
    the CPU oracle (gradients of all ranks are gathered with NCCL only to build the expectation);
 2. the NIC command interface on the GPU backend (10 requests, 8 done slots, in order);
 3. the native DP trainer: replicas bit-identical after several steps, loss falls, and the weights
-   match a CPU oracle run of the same data-parallel SGD within bf16 GEMM tolerance.
+   match a CPU oracle run of the same data-parallel SGD within bf16 GEMM tolerance;
+   3b. gradient buckets of several layers, the compressed GEMM epilogue and the GEMM -> reduce-scatter
+   epilogue give the same bits as one call per layer on fp32 gradients;
+4. start-up plumbing: parameter broadcast from rank 0, scatter of a global minibatch
+   (the reference's MPI_Bcast / MPI_Scatter, sw/mlp_mpi_example_f32.cpp:453-470).
 Prints one JSON line per check on rank 0 and exits non-zero on failure.
 """
 import json
@@ -268,6 +272,28 @@ for codec in ("f32", "bfp"):
             timeouts=comm.counters()["timeouts"])
         if not same:
             fails.append(("mlp_bucketed", codec, bucket_mb, fusec))
+
+# ------------------------------------------------------------------ 4. start-up plumbing: Bcast of parameters, Scatter of a batch
+cfg = MLPConfig(sizes=[256, 256, 128], mb=64, codec="f32")
+tr = MLPTrainer(cfg, comm=comm)
+ref_w = [tr.buffer("weight", l).clone() for l in range(cfg.nlayers)]
+if rank != 0:
+    for l in range(cfg.nlayers):
+        tr.buffer("weight", l).add_(1.0 + rank)          # diverge on purpose
+tr.broadcast_parameters(0)
+ok = all(torch.equal(tr.buffer("weight", l), ref_w[l]) for l in range(cfg.nlayers))
+ok &= all(torch.equal(tr.buffer("shadow", l), ref_w[l].bfloat16()) for l in range(cfg.nlayers))
+gx = torch.arange(world * cfg.mb * 256, dtype=torch.float32).reshape(world * cfg.mb, 256) % 251 if rank == 0 else None
+gy = (torch.arange(world * cfg.mb, dtype=torch.int32) % 128) if rank == 0 else None
+xs, ys = tr.scatter_batch(gx, gy, 0)
+want_x = (torch.arange(world * cfg.mb * 256, dtype=torch.float32).reshape(world, cfg.mb, 256) % 251)[rank].bfloat16()
+want_y = (torch.arange(world * cfg.mb, dtype=torch.int32) % 128).reshape(world, cfg.mb)[rank]
+ok &= torch.equal(xs.cpu(), want_x) and torch.equal(ys.cpu(), want_y)
+ok = all_ok(bool(ok))
+say(check="bcast_scatter", ok=ok)
+if not ok:
+    fails.append(("bcast_scatter",))
+tr.close()
 
 if world > 1:
     dist.barrier()
