@@ -47,6 +47,40 @@ struct EpiParams {
 // Output selector of the epilogue.
 constexpr int OUT_BF16 = 0, OUT_FP32 = 1, OUT_COMPRESSED = 2;
 
+// 32 fp32 values of one row -> two BFP16x8 blocks: w[0..7] = int8 mantissas, return = the two shared
+// exponents (low byte first).  Same bits as bfp_exp_field / bfp_quant value by value; the rounding mode
+// is a template parameter so the per-value code has no branch, and the shared exponent comes from one
+// integer max over the magnitudes (the exponent field is their top byte).
+template <int MODE>
+__device__ __forceinline__ uint32_t bfp_pack32(const float (&v)[32], uint32_t (&w)[8]) {
+  uint32_t exps = 0;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint32_t mag = 0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) mag = max(mag, __float_as_uint(v[16 * h + j]) & 0x7FFFFFFFu);
+    const uint32_t E = mag >> 23;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int32_t q = MODE == AINIC_BFP_HW_EXACT ? bfp_quant_hw(__float_as_uint(v[16 * h + j]), E) : bfp_quant_clean(v[16 * h + j], E);
+      w[4 * h + (j >> 2)] |= ((uint32_t)q & 0xFFu) << (8 * (j & 3));
+    }
+    exps |= E << (8 * h);
+  }
+  return exps;
+}
+
+// Where frame `frame` of this GEMM's output goes: the local buffer, or (reduce-scatter epilogue) the
+// inbox of the rank that owns it.
+__device__ __forceinline__ uint8_t* frame_dst(const EpiParams& ep, size_t frame, size_t fbytes) {
+  if (ep.push_n > 1) {
+    const uint32_t F = ep.push_frame0 + (uint32_t)frame;
+    const uint32_t owner = F / ep.push_shard;
+    return ep.push[owner] + ((size_t)ep.push_rank * ep.push_shard + (F - owner * ep.push_shard)) * fbytes;
+  }
+  return ep.cgrad + frame * fbytes;
+}
+
 // 32 consecutive values of one row -> two BFP16x8 blocks or one MXFP8 block, written straight into
 // the frame layout the all-reduce kernels read (512 mantissa bytes + 32 exponent / 16 scale bytes
 // per 512 values, csrc/common/bfp_codec.h).  This is the reference's BFP adapter sitting directly
@@ -56,27 +90,12 @@ __device__ __forceinline__ void store_compressed32(const EpiParams& ep, size_t i
   const size_t frame = idx >> 9;
   const uint32_t off = (uint32_t)(idx & 511);
   const size_t fbytes = ep.codec == AINIC_CODEC_BFP ? (size_t)kBfpFrameBytes : (size_t)kMxFrameBytes;
-  uint8_t* fr;
-  if (ep.push_n > 1) {  // the frame's owner reduces it: store it there (NVLink store, fire and forget)
-    const uint32_t F = ep.push_frame0 + (uint32_t)frame;
-    const uint32_t owner = F / ep.push_shard;
-    fr = ep.push[owner] + ((size_t)ep.push_rank * ep.push_shard + (F - owner * ep.push_shard)) * fbytes;
-  } else {
-    fr = ep.cgrad + frame * fbytes;
-  }
+  uint8_t* fr = frame_dst(ep, frame, fbytes);
   if (ep.codec == AINIC_CODEC_BFP) {
-    uint32_t exps = 0;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      uint32_t E = 0;
-#pragma unroll
-      for (int j = 0; j < 16; ++j) E = max(E, bfp_exp_field(__float_as_uint(v[16 * h + j])));
-      uint32_t w[4] = {0, 0, 0, 0};
-#pragma unroll
-      for (int j = 0; j < 16; ++j) w[j >> 2] |= ((uint32_t)bfp_quant(v[16 * h + j], E, ep.bfp_mode) & 0xFFu) << (8 * (j & 3));
-      *reinterpret_cast<uint4*>(fr + off + 16 * h) = make_uint4(w[0], w[1], w[2], w[3]);
-      exps |= E << (8 * h);
-    }
+    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const uint32_t exps = ep.bfp_mode == AINIC_BFP_HW_EXACT ? bfp_pack32<AINIC_BFP_HW_EXACT>(v, w) : bfp_pack32<AINIC_BFP_CLEAN>(v, w);
+    *reinterpret_cast<uint4*>(fr + off) = make_uint4(w[0], w[1], w[2], w[3]);
+    *reinterpret_cast<uint4*>(fr + off + 16) = make_uint4(w[4], w[5], w[6], w[7]);
     *reinterpret_cast<uint16_t*>(fr + kBfpExpOff + (off >> 4)) = (uint16_t)exps;
   } else {  // MXFP8
     uint32_t E = 0;
@@ -91,6 +110,111 @@ __device__ __forceinline__ void store_compressed32(const EpiParams& ep, size_t i
     *reinterpret_cast<uint4*>(fr + off + 16) = make_uint4(w[4], w[5], w[6], w[7]);
     fr[kMxScaleOff + (off >> 5)] = (uint8_t)sb;
   }
+}
+
+// Compressed epilogue through shared memory.  A tcgen05.ld lane owns ONE ROW of the accumulator, so
+// writing frames straight from registers makes every store instruction of a warp touch 32 different
+// frames, 16 bytes each - tolerable in local HBM, hopeless as NVLink write packets.  Here each
+// epilogue warp first parks the quantised bytes of its 32 rows x BLOCK_N columns in shared memory
+// (16-byte units XOR-swizzled by row: conflict-free both ways), then writes them out with
+// consecutive lanes on consecutive 16-byte units of the same row: BLOCK_N contiguous bytes per row
+// (half a frame for BLOCK_N = 256).  The exponent / scale bytes of a row's chunks are collected in
+// registers and leave as one vector store per row when rows are whole frames (ldc % 512 == 0).
+// stage = this warp's 32 * BLOCK_N bytes; row0 = first row of this warp; 512 % BLOCK_N == 0.
+template <int BLOCK_N>
+__device__ __forceinline__ void epilogue_store_frames(const EpiParams& ep, uint32_t taddr, int row0, int n0, uint8_t* stage, int lane) {
+  static_assert(512 % BLOCK_N == 0 && BLOCK_N >= 128, "row spans must not straddle frames");
+  constexpr int kChunks = BLOCK_N / 32;
+  constexpr int kUnits = BLOCK_N / 16;          // 16-byte units per row
+  const bool bfp = ep.codec == AINIC_CODEC_BFP;
+  const size_t fbytes = bfp ? (size_t)kBfpFrameBytes : (size_t)kMxFrameBytes;
+  uint32_t side[kChunks / 2];   // BFP: 2 exponent bytes per chunk; MX: 1 scale byte per chunk (half of it used)
+#pragma unroll
+  for (int i = 0; i < kChunks / 2; ++i) side[i] = 0;
+  // one chunk (32 columns of this lane's row): quantise, park the 32 bytes in shared memory
+  auto process = [&](const uint32_t (&r)[32], int c) {
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * ep.alpha;
+    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t sb;
+    if (bfp) {
+      sb = ep.bfp_mode == AINIC_BFP_HW_EXACT ? bfp_pack32<AINIC_BFP_HW_EXACT>(v, w) : bfp_pack32<AINIC_BFP_CLEAN>(v, w);
+      // kChunks * 2 bytes per row, packed little-endian in chunk order
+      if (c & 1) side[c >> 1] |= sb << 16; else side[c >> 1] |= sb;
+    } else {
+      uint32_t mag = 0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) mag = max(mag, __float_as_uint(v[j]) & 0x7FFFFFFFu);
+      sb = mx_scale_byte(mag >> 23);
+      const float inv = mx_inv_scale(sb);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) w[j >> 2] |= f32_to_e4m3(v[j] * inv) << (8 * (j & 3));
+      side[c >> 2] |= sb << (8 * (c & 3));
+    }
+    uint4* srow = reinterpret_cast<uint4*>(stage) + lane * kUnits;
+    srow[(2 * c) ^ (lane & (kUnits - 1))] = make_uint4(w[0], w[1], w[2], w[3]);
+    srow[(2 * c + 1) ^ (lane & (kUnits - 1))] = make_uint4(w[4], w[5], w[6], w[7]);
+  };
+  // the TMEM read of chunk c + 1 is in flight while chunk c is quantised (two register buffers)
+  uint32_t ra[32], rb[32];
+  tmem_ld_32x32b_x32(taddr, ra);
+#pragma unroll
+  for (int c = 0; c < kChunks; c += 2) {
+    tmem_ld_wait();
+    tmem_ld_32x32b_x32(taddr + (c + 1) * 32, rb);
+    process(ra, c);
+    tmem_ld_wait();
+    if (c + 2 < kChunks) tmem_ld_32x32b_x32(taddr + (c + 2) * 32, ra);
+    process(rb, c + 1);
+  }
+  __syncwarp();
+  // ---- mantissas: 32 lanes x 16 B per instruction = 32 / kUnits whole row segments
+  if (n0 < ep.N) {
+#pragma unroll 1
+    for (int i = 0; i < kUnits; ++i) {
+      const int idx = i * 32 + lane;
+      const int rr = idx / kUnits, u = idx % kUnits;
+      const int grow = row0 + rr;
+      if (grow < ep.M && n0 + u * 16 < ep.N) {
+        const uint4 q = reinterpret_cast<const uint4*>(stage)[rr * kUnits + (u ^ (rr & (kUnits - 1)))];
+        const size_t flat = (size_t)grow * ep.ldc + n0 + u * 16;
+        *reinterpret_cast<uint4*>(frame_dst(ep, flat >> 9, fbytes) + (flat & 511)) = q;
+      }
+    }
+    // ---- exponents / scales of this lane's own row
+    const int grow = row0 + lane;
+    if (grow < ep.M) {
+      const size_t flat = (size_t)grow * ep.ldc + n0;
+      if ((ep.ldc & 511) == 0 && n0 + BLOCK_N <= ep.N) {
+        uint8_t* fr = frame_dst(ep, flat >> 9, fbytes);
+        const uint32_t off = (uint32_t)(flat & 511);
+        if (bfp) {  // kChunks * 2 bytes at exponent offset off / 16
+          uint8_t* d = fr + kBfpExpOff + (off >> 4);
+          if constexpr (kChunks == 8) *reinterpret_cast<uint4*>(d) = make_uint4(side[0], side[1], side[2], side[3]);
+          else if constexpr (kChunks == 4) *reinterpret_cast<uint2*>(d) = make_uint2(side[0], side[1]);
+          else *reinterpret_cast<uint32_t*>(d) = side[0];
+        } else {    // kChunks bytes at scale offset off / 32
+          uint8_t* d = fr + kMxScaleOff + (off >> 5);
+          if constexpr (kChunks == 8) *reinterpret_cast<uint2*>(d) = make_uint2(side[0], side[1]);
+          else if constexpr (kChunks == 4) *reinterpret_cast<uint32_t*>(d) = side[0];
+          else *reinterpret_cast<uint16_t*>(d) = (uint16_t)side[0];
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+          if (n0 + c * 32 < ep.N) {
+            const size_t f2 = flat + c * 32;
+            uint8_t* fr = frame_dst(ep, f2 >> 9, fbytes);
+            const uint32_t off = (uint32_t)(f2 & 511);
+            if (bfp) *reinterpret_cast<uint16_t*>(fr + kBfpExpOff + (off >> 4)) = (uint16_t)(side[c >> 1] >> (16 * (c & 1)));
+            else fr[kMxScaleOff + (off >> 5)] = (uint8_t)(side[c >> 2] >> (8 * (c & 3)));
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();   // the staging area is reused by this warp's next tile
 }
 
 // Shared-memory matrix descriptor (sm_100 format, version 1, SWIZZLE_128B).

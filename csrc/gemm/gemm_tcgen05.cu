@@ -26,6 +26,12 @@ __host__ __device__ constexpr int stage_bytes(int block_n) { return BLOCK_M * BL
 __host__ __device__ constexpr int num_stages(int block_n) {
   return (kSmemBudget / stage_bytes(block_n)) > 8 ? 8 : (kSmemBudget / stage_bytes(block_n));
 }
+// Compressed output of tiles whose rows never straddle a frame is staged through shared memory
+// (epilogue_store_frames): 32 * block_n bytes for each of the four epilogue warps.
+__host__ __device__ constexpr bool staged_frames(int block_n, int out) {
+  return out == OUT_COMPRESSED && 512 % block_n == 0 && block_n >= 128;
+}
+__host__ __device__ constexpr int staging_bytes(int block_n, int out) { return staged_frames(block_n, out) ? 4 * 32 * block_n : 0; }
 __host__ __device__ constexpr uint32_t tmem_cols(int block_n) {
   return 2 * block_n <= 32 ? 32u : 2 * block_n <= 64 ? 64u : 2 * block_n <= 128 ? 128u : 2 * block_n <= 256 ? 256u : 512u;
 }
@@ -152,7 +158,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       mbar_wait_backoff(&tmem_full[acc], acc_phase, (uint32_t)ep.epi_sleep);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N);
-      epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
+      if constexpr (staged_frames(BLOCK_N, OUT_F32)) {
+        if (epi_warps == 4) {   // compressed frames leave through shared memory, whole row segments at a time
+          uint8_t* stage = smem + kStages * (kABytes + kBBytes) + 256 + (warp - 2) * (32 * BLOCK_N);
+          epilogue_store_frames<BLOCK_N>(ep, taddr, m0 + quarter * 32, n0, stage, lane);
+        } else {
+          epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
+        }
+      } else {
+        epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
@@ -182,7 +197,8 @@ static int launch(const void* a, int lda, const void* b, int ldb, const EpiParam
   else rc = cached_tmap(&tb, b, ep.N, ep.K, ldb, BLOCK_K, BLOCK_N);
   if (rc) return rc;
   auto kern = gemm_kernel<BLOCK_N, A_MN, B_MN, OUT_F32>;
-  constexpr int smem = num_stages(BLOCK_N) * stage_bytes(BLOCK_N) + 1024 + 256;
+  constexpr int smem = num_stages(BLOCK_N) * stage_bytes(BLOCK_N) + 1024 + 256 + staging_bytes(BLOCK_N, OUT_F32);
+  static_assert(smem <= 227 * 1024, "shared memory budget");
   static bool configured = false;
   if (!configured) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return AINIC_ERR_CUDA;
