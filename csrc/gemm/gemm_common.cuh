@@ -42,6 +42,7 @@ struct EpiParams {
   uint8_t* push[AINIC_MAX_RANKS];
   int push_n, push_rank;   // push_n <= 1: frames go to cgrad
   uint32_t push_shard, push_frame0;
+  int stage_frames;        // compressed output leaves through shared memory (epilogue_store_frames)
 };
 
 // Output selector of the epilogue.

@@ -159,7 +159,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N);
       if constexpr (staged_frames(BLOCK_N, OUT_F32)) {
-        if (epi_warps == 4) {   // compressed frames leave through shared memory, whole row segments at a time
+        if (epi_warps == 4 && ep.stage_frames) {   // compressed frames leave through shared memory, whole row segments at a time
           uint8_t* stage = smem + kStages * (kABytes + kBBytes) + 256 + (warp - 2) * (32 * BLOCK_N);
           epilogue_store_frames<BLOCK_N>(ep, taddr, m0 + quarter * 32, n0, stage, lane);
         } else {
@@ -277,6 +277,15 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
       ep.cgrad = ep.push[sc->rank];   // selects the compressed epilogue
       if (sc->nranks == 1) { ep.cgrad += (size_t)sc->frame0 * (ep.codec == AINIC_CODEC_BFP ? 544 : 528); }
     }
+  }
+  // Staging through shared memory pays for itself when the stores cross NVLink (scatter).  For local
+  // frames it is opt-in (AINIC_GEMM_STAGE_FRAMES=1): alone on the GPU it is as fast as the direct path
+  // (24.6 vs 25.6 us on the reference layer), inside the training step it is slower (2 ranks, same
+  // box, A/B/A/B: 0.680 vs 0.647 ms/step) - 143 registers and 32 KB more shared memory per CTA leave
+  // less room for the all-reduce CTAs that share the SMs.
+  {
+    static const int stage_env = getenv("AINIC_GEMM_STAGE_FRAMES") ? atoi(getenv("AINIC_GEMM_STAGE_FRAMES")) : -1;
+    ep.stage_frames = stage_env >= 0 ? stage_env : (ep.push_n > 1 ? 1 : 0);
   }
   if (ep.cgrad) {  // compressed gradient output: backward-weight layout only, whole 32-value groups
     if (layout != AINIC_GEMM_TN || (N % 32) || (ldc % 32) || ((uintptr_t)ep.cgrad & 15) ||
