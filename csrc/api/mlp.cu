@@ -126,11 +126,11 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
     m->fuse_compress = mode >= 1 && n > 1 && (codec == AINIC_CODEC_BFP || codec == AINIC_CODEC_MXFP8);
     // AINIC_FUSE_COMPRESS=2: the epilogue also performs the reduce-scatter's data movement - each frame
     // is stored into the inbox of the rank that owns it, over NVLink, while the GEMM is still running.
-    // Bit-identical results (scripts/mp_check.py 3b), but measured SLOWER: 1.39 vs 0.80 ms/step at 8
-    // ranks, 0.81 vs 0.71 at 2.  A thread of the epilogue owns 32 values of one row (tcgen05.ld
-    // 32x32b), so a warp's stores are 32 separate 16-byte pieces of 32 different frames; over NVLink
-    // those are tiny write packets and the epilogue stalls on them.  Opt-in until the tile is
-    // transposed through shared memory into whole 544-byte frames.
+    // Bit-identical results (scripts/mp_check.py 3b).  The frames are staged through shared memory and
+    // leave as whole row segments (epilogue_store_frames); stored straight from the tcgen05.ld register
+    // layout - 16-byte pieces of 32 different frames per warp instruction - the same epilogue was 1.7x
+    // slower.  Measured (ms/step, compressed epilogue + pull -> scatter): 2 ranks 0.682 -> 0.673, 4 ranks
+    // 0.748 -> 0.707; not yet measured at 8 ranks, hence opt-in.
     m->fuse_scatter = m->fuse_compress && mode == 2;
   }
   m->layers.resize(nlayers);
