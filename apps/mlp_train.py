@@ -10,7 +10,11 @@
   (:590-680 used MPI_Iallreduce + libxsmm opt_exec); F = forward only (:543-588).
 * ``bn bk bc`` are libxsmm blocking factors: accepted for compatibility, meaningless for tcgen05 tiles.
 * env: AINIC_CODEC (auto|f32|bfp|mxfp8|bf16), AINIC_ALGO (auto|oneshot|twoshot|ring), AINIC_LR (0.1),
-  DETAILED_PROFILE=1 (per-phase device times), CHECKPOINT=path (save at the end, resume if present).
+  DETAILED_PROFILE=1 (per-phase device times), CHECKPOINT=path (save at the end, resume if present),
+  AINIC_BUCKET_MB (fp32 MiB of gradients per fused call; 0 = one call per layer like the reference),
+  AINIC_MLP_GRAPH=0 (direct launches instead of replaying the step as a CUDA graph),
+  AINIC_FUSE_COMPRESS=0|1|2 (weight-gradient GEMM epilogue: fp32 / wire-format frames / frames stored
+  into the reducing rank's memory).
 Output: the reference's block (GFLOP / fp time / GFLOPS / PERFDUMP / profile lines, :794-816).
 """
 import os

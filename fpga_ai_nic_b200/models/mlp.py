@@ -59,6 +59,20 @@ class MLPConfig:
             return float(os.environ["AINIC_BUCKET_MB"])
         return 80.0 if world >= 2 else 0.0
 
+    def bucket_plan(self, world: int = 1) -> list:
+        """(lowest layer, highest layer) of every fused all-reduce call of one step, in issue order - the
+        same walk csrc/api/mlp.cu does: collect layers from the last one down until the bucket holds
+        ``bucket_mb`` of fp32 gradients (layer 0 always closes the last bucket)."""
+        limit = int(self.resolved_bucket_mb(world) * (1 << 20))
+        plan, top, pend = [], self.nlayers - 1, 0
+        for l in range(self.nlayers - 1, -1, -1):
+            pend += self.sizes[l] * self.sizes[l + 1] * 4
+            if l > 0 and pend < limit:
+                continue
+            plan.append((l, top))
+            top, pend = l - 1, 0
+        return plan
+
     def heap_bytes(self, world: int = 8) -> int:
         p = self.param_count() + 1024 * self.nlayers
         biggest = max(self.sizes[l] * self.sizes[l + 1] for l in range(self.nlayers))

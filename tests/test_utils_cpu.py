@@ -53,3 +53,27 @@ def test_launcher_two_ranks_gloo(tmp_path):
 def test_bench_reference_arm_reports_unavailable():
     p = subprocess.run([sys.executable, "bench.py", "--impl", "reference"], capture_output=True, text=True, cwd=launcher.ROOT)
     assert p.returncode == 0 and '"impl": "reference"' in p.stdout and "unavailable" in p.stdout
+
+
+def test_bucket_plan_and_heap_sizing(monkeypatch):
+    """Gradient buckets: per layer on one rank (the reference's behaviour, :754), 80 MiB with peers,
+    explicit / environment overrides; the heap must hold the staging of the largest bucket."""
+    monkeypatch.delenv("AINIC_BUCKET_MB", raising=False)
+    cfg = MLPConfig.reference()                                    # 10 layers x 16 MiB
+    assert cfg.bucket_plan(1) == [(l, l) for l in range(9, -1, -1)]
+    assert cfg.bucket_plan(8) == [(5, 9), (0, 4)]
+    assert MLPConfig(sizes=[2048] * 11, bucket_mb=48).bucket_plan(8) == [(7, 9), (4, 6), (1, 3), (0, 0)]
+    assert MLPConfig(sizes=[2048] * 11, bucket_mb=1e6).bucket_plan(2) == [(0, 9)]
+    assert MLPConfig(sizes=[8192] * 9).bucket_plan(8) == [(l, l) for l in range(7, -1, -1)]   # 256 MiB layers
+    monkeypatch.setenv("AINIC_BUCKET_MB", "32")
+    assert cfg.bucket_plan(1) == [(8, 9), (6, 7), (4, 5), (2, 3), (0, 1)]
+    assert MLPConfig(sizes=[2048] * 11, bucket_mb=0).bucket_plan(8) == [(l, l) for l in range(9, -1, -1)]
+    monkeypatch.delenv("AINIC_BUCKET_MB")
+    # every plan covers each layer exactly once, top down
+    for world, mb in ((1, None), (2, None), (8, 20.0), (8, 100.0)):
+        plan = MLPConfig(sizes=[256, 512, 384, 128, 640], bucket_mb=mb).bucket_plan(world)
+        covered = [l for lo, hi in plan for l in range(hi, lo - 1, -1)]
+        assert covered == list(range(3, -1, -1))
+    p = cfg.param_count()
+    assert cfg.heap_bytes(1) >= p * 8 and cfg.heap_bytes(8) > cfg.heap_bytes(1)
+    assert MLPConfig(sizes=[2048] * 11, bucket_mb=1e6).heap_bytes(8) > cfg.heap_bytes(8)
