@@ -78,6 +78,43 @@ def oneshot_precompressed(w, r, b, calls, double_buffer=True):
             yield
 
 
+def twoshot_scattered(w, r, b, calls, double_buffer=True, start_barrier=True):
+    """GEMM -> reduce-scatter epilogue + two-shot (precompressed == 2): before the launch this rank's GEMM
+    stores its frames of every shard into the OWNER's inbox (slot [my rank]); the kernel's first flag
+    exchange tells the owners that the stores are complete; the reduce phase reads the local inbox."""
+    if not hasattr(w, "inbox"):
+        w.inbox = [[[[0] * w.ctas for _ in range(w.n)] for _ in range(2)] for _ in range(w.n)]   # [owner][parity][src][cta]
+    for epoch in range(1, calls + 1):
+        par = (epoch & 1) if double_buffer else 0
+        for p in range(w.n):                               # weight-gradient GEMM epilogue: NVLink stores
+            w.inbox[p][par][r][b] = epoch
+            yield
+        for p in range(w.n):
+            if p != r:
+                w.flags[p][0][r][b] = epoch
+                yield
+        if start_barrier:
+            while any(w.flags[r][0][p][b] < epoch for p in range(w.n) if p != r):
+                yield
+        for p in range(w.n):                               # reduce my shard: local reads only
+            if w.inbox[r][par][p][b] != epoch:
+                raise Violation(f"rank {r} cta {b} call {epoch}: inbox slot of rank {p} holds call {w.inbox[r][par][p][b]}")
+            yield
+        w.stage_d[r][b] = epoch
+        yield
+        for p in range(w.n):
+            if p != r:
+                w.flags[p][1][r][b] = epoch
+                yield
+        while any(w.flags[r][1][p][b] < epoch for p in range(w.n) if p != r):
+            yield
+        for p in range(w.n):
+            if p != r:
+                if w.stage_d[p][b] != epoch:
+                    raise Violation(f"rank {r} cta {b} call {epoch}: stage D of rank {p} holds call {w.stage_d[p][b]}")
+                yield
+
+
 def run(body, n, ctas, calls, seed, **kw):
     rng = random.Random(seed)
     w = World(n, ctas)
@@ -109,6 +146,16 @@ def test_precompressed_oneshot_is_safe_with_two_buffers(n):
         run(oneshot_precompressed, n, 2, 6, seed)
 
 
+@pytest.mark.parametrize("n", [2, 4, 8])
+@pytest.mark.parametrize("double_buffer", [True, False])
+def test_scattered_twoshot_is_safe(n, double_buffer):
+    """Safe even with ONE inbox as long as a rank's next GEMM runs after its own previous call on that
+    bucket (the trainer's `updated` dependency): the second flag exchange orders it after every owner's
+    reads.  The two inboxes per bucket are margin for callers that relax that dependency."""
+    for seed in range(30):
+        run(twoshot_scattered, n, 2, 6, seed, double_buffer=double_buffer)
+
+
 def _caught(body, **kw):
     hits = 0
     for seed in range(60):
@@ -125,6 +172,8 @@ def test_negative_controls_are_caught():
     # with a single GEMM output buffer and no closing barrier a fast rank's next step overwrites frames a
     # slow rank is still reading
     assert _caught(oneshot_precompressed, double_buffer=False) > 0
+    # scattered input: without the first exchange an owner reduces slots its peers have not stored yet
+    assert _caught(twoshot_scattered, start_barrier=False) > 0
 
 
 def test_twoshot_alone_would_not_need_the_parity_halves():
