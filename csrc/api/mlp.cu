@@ -129,8 +129,8 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
     // Bit-identical results (scripts/mp_check.py 3b).  The frames are staged through shared memory and
     // leave as whole row segments (epilogue_store_frames); stored straight from the tcgen05.ld register
     // layout - 16-byte pieces of 32 different frames per warp instruction - the same epilogue was 1.7x
-    // slower.  Measured (ms/step, compressed epilogue + pull -> scatter): 2 ranks 0.682 -> 0.673, 4 ranks
-    // 0.748 -> 0.707; not yet measured at 8 ranks, hence opt-in.
+    // slower.  Measured: about level with the compressed epilogue + pull at 2 and 4 ranks
+    // (profiles/README.md section 1), not yet measured at 8 ranks, hence opt-in.
     m->fuse_scatter = m->fuse_compress && mode == 2;
   }
   m->layers.resize(nlayers);
