@@ -15,10 +15,12 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <string>
 #include <vector>
 
 #include "../../include/ainic.h"
+#include "bucket_plan.h"
 
 namespace {
 
@@ -72,6 +74,8 @@ struct ainic_mlp {
   __nv_bfloat16* wb_arena = nullptr;
   uint8_t* cg_arena[2] = {nullptr, nullptr};
   size_t bucket_bytes = 0;
+  std::vector<int> bucket_layers;    // optional explicit schedule: layers per bucket from the last layer down
+                                     // (AINIC_BUCKET_LAYERS="4,3,2,1"); overrides bucket_bytes when non-empty
   // CUDA-graph replay of the whole iteration (one launch per step instead of ~30 kernel launches and
   // ~100 event operations).  One instantiated graph per (input, labels, loss, parity) tuple.
   struct StepGraph {
@@ -188,6 +192,15 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
     const int n = ainic_comm_size(comm);
     m->bucket_bytes = n >= 2 ? (size_t)80 << 20 : 0;
     if (const char* e = getenv("AINIC_BUCKET_MB")) m->bucket_bytes = (size_t)(atof(e) * 1048576.0);
+    if (const char* e = getenv("AINIC_BUCKET_LAYERS")) {   // e.g. "4,3,2,1": big buckets first, a small exposed tail
+      for (const char* p = e; *p;) {
+        char* end = nullptr;
+        const long v = strtol(p, &end, 10);
+        if (end == p) break;
+        if (v > 0) m->bucket_layers.push_back((int)v);
+        p = *end ? end + 1 : end;
+      }
+    }
   }
   TRY(ainic_comm_reserve(comm, max_bucket_count(m)));
   // Graph replay is on by default (AINIC_MLP_GRAPH=0 switches it off).  It needs launch arguments that do
@@ -271,16 +284,23 @@ extern "C" int ainic_mlp_sync_shadows(ainic_mlp_t* m, void* stream) {
 
 extern "C" unsigned long long ainic_mlp_launches(ainic_mlp_t* m) { return m ? m->launches : 0; }
 // Largest bucket (in values, arena pads included) the current bucket size produces.
+// Bucket plan (csrc/api/bucket_plan.h): blo[l] / bhi[l] = lowest / highest layer of l's bucket.
+static void plan_buckets(const ainic_mlp* m, std::vector<int>& blo, std::vector<int>& bhi) {
+  std::vector<size_t> bytes(m->nlayers);
+  for (int l = 0; l < m->nlayers; ++l) bytes[l] = (size_t)m->layers[l].in * m->layers[l].out * 4;
+  ainic::plan_buckets(bytes, m->bucket_bytes, m->bucket_layers, blo, bhi);
+}
+static size_t bucket_values(const ainic_mlp* m, int lo, int hi) {   // arena pads included, last layer exact
+  size_t count = 0;
+  for (int k = lo; k < hi; ++k) count += m->layers[k].slot;
+  return count + (size_t)m->layers[hi].in * m->layers[hi].out;
+}
 static size_t max_bucket_count(const ainic_mlp* m) {
-  size_t best = 0, count = 0, pending = 0;
-  for (int l = m->nlayers - 1; l >= 0; --l) {
-    const Layer& L = m->layers[l];
-    count += L.slot;
-    pending += (size_t)L.in * L.out * 4;
-    if (l > 0 && pending < m->bucket_bytes) continue;
-    if (count > best) best = count;
-    count = pending = 0;
-  }
+  std::vector<int> blo, bhi;
+  plan_buckets(m, blo, bhi);
+  size_t best = 0;
+  for (int l = 0; l < m->nlayers; ++l)
+    if (blo[l] == l) best = std::max(best, bucket_values(m, l, bhi[l]));
   return best;
 }
 // Gradient bucket size in fp32 bytes (0 = one all-reduce per layer).  Takes effect at the next step;
@@ -349,24 +369,9 @@ static int step_body(ainic_mlp* m, const void* x_bf16, const int32_t* labels, fl
     m->launches++;
   }
   if (m->profile) TRY_CUDA(cudaEventRecord(m->prof[2], s));
-  // bucket plan (walk down from the last layer): blo[l] / bhi[l] = lowest / highest layer of l's bucket
-  std::vector<int> blo(Ln), bhi(Ln);
-  {
-    int top = Ln - 1;
-    size_t pend = 0;
-    for (int l = Ln - 1; l >= 0; --l) {
-      pend += (size_t)m->layers[l].in * m->layers[l].out * 4;
-      if (l > 0 && pend < m->bucket_bytes) continue;
-      for (int k = l; k <= top; ++k) { blo[k] = l; bhi[k] = top; }
-      top = l - 1;
-      pend = 0;
-    }
-  }
-  auto bucket_count = [&](int lo, int hi) {
-    size_t count = 0;
-    for (int k = lo; k < hi; ++k) count += m->layers[k].slot;
-    return count + (size_t)m->layers[hi].in * m->layers[hi].out;
-  };
+  std::vector<int> blo, bhi;
+  plan_buckets(m, blo, bhi);
+  auto bucket_count = [&](int lo, int hi) { return bucket_values(m, lo, hi); };
   const int nranks = ainic_comm_size(m->comm), rank = ainic_comm_rank(m->comm);
   for (int l = Ln - 1; l >= 0; --l) {
     Layer& L = m->layers[l];

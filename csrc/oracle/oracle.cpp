@@ -1,6 +1,7 @@
 // CPU oracle implementation.  See oracle.h for what each entry models and where in the
 // reference the behaviour comes from.
 #include "oracle.h"
+#include "../api/bucket_plan.h"
 
 #include <math.h>
 #include <stdlib.h>
@@ -184,6 +185,14 @@ extern "C" void ainic_ref_allreduce_twoshot(const float* grads, int nranks, size
   ainic_ref_allreduce_oneshot(grads, nranks, count, codec, mode, out);
   codec_roundtrip(out, count, codec, mode);
   for (int r = 1; r < nranks; ++r) memcpy(out + (size_t)r * count, out, count * sizeof(float));
+}
+
+extern "C" void ainic_ref_bucket_plan(int nlayers, const size_t* layer_bytes, size_t bucket_bytes, const int* schedule,
+                                      int nsched, int* lo, int* hi) {
+  std::vector<size_t> bytes(layer_bytes, layer_bytes + nlayers);
+  std::vector<int> sched(schedule ? schedule : nullptr, schedule ? schedule + nsched : nullptr), vlo, vhi;
+  ainic::plan_buckets(bytes, bucket_bytes, sched, vlo, vhi);
+  for (int l = 0; l < nlayers; ++l) { lo[l] = vlo[l]; hi[l] = vhi[l]; }
 }
 
 extern "C" void ainic_ref_sgd(float* w, const float* g, size_t count, float lr) {

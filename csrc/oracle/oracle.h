@@ -43,6 +43,10 @@ void ainic_ref_allreduce_twoshot(const float* grads, int nranks, size_t count, i
                                  float* out);
 // w[i] = fmaf(-lr, g[i], w[i])  (hw/weight_update.sv:440-452 with a runtime lr).
 void ainic_ref_sgd(float* w, const float* g, size_t count, float lr);
+/* Gradient bucket plan of the GPU trainer (csrc/api/bucket_plan.h): lo[l] / hi[l] = lowest / highest layer
+ * of layer l's bucket.  schedule (nullable, nsched entries) = layers per bucket from the last layer down. */
+void ainic_ref_bucket_plan(int nlayers, const size_t* layer_bytes, size_t bucket_bytes, const int* schedule, int nsched,
+                           int* lo, int* hi);
 
 // ---- MLP (sw/mlp_mpi_example_f32.cpp) ---------------------------------------
 // Row-major everywhere.  W[l] is [C[l+1]][C[l]] (out x in).  fuse: 0 none, 1 bias, 2 relu, 3 bias+relu.

@@ -77,6 +77,8 @@ def oracle() -> C.CDLL:
     lib.ainic_ref_allreduce_oneshot.argtypes = [vp, C.c_int, sz, C.c_int, C.c_int, vp]
     lib.ainic_ref_allreduce_twoshot.argtypes = [vp, C.c_int, sz, C.c_int, C.c_int, vp]
     lib.ainic_ref_sgd.argtypes = [vp, vp, sz, C.c_float]
+    lib.ainic_ref_bucket_plan.restype = None
+    lib.ainic_ref_bucket_plan.argtypes = [C.c_int, vp, sz, vp, C.c_int, vp, vp]
     lib.ainic_ref_fc_fwd.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int]
     lib.ainic_ref_fc_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int]
     lib.ainic_ref_softmax_loss.restype = C.c_float

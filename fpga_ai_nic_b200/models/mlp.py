@@ -61,16 +61,23 @@ class MLPConfig:
 
     def bucket_plan(self, world: int = 1) -> list:
         """(lowest layer, highest layer) of every fused all-reduce call of one step, in issue order - the
-        same walk csrc/api/mlp.cu does: collect layers from the last one down until the bucket holds
-        ``bucket_mb`` of fp32 gradients (layer 0 always closes the last bucket)."""
+        same walk csrc/api/bucket_plan.h does: collect layers from the last one down until the bucket
+        holds ``bucket_mb`` of fp32 gradients, or follow the explicit schedule AINIC_BUCKET_LAYERS
+        ("4,3,2,1" = layers per bucket, big buckets first); layer 0 always closes the last bucket."""
         limit = int(self.resolved_bucket_mb(world) * (1 << 20))
-        plan, top, pend = [], self.nlayers - 1, 0
+        sched = [int(v) for v in os.environ.get("AINIC_BUCKET_LAYERS", "").replace(",", " ").split() if int(v) > 0]
+        plan, top, pend, n_in, si = [], self.nlayers - 1, 0, 0, 0
         for l in range(self.nlayers - 1, -1, -1):
             pend += self.sizes[l] * self.sizes[l + 1] * 4
-            if l > 0 and pend < limit:
+            n_in += 1
+            if sched:
+                close = n_in >= (sched[si] if si < len(sched) else 1)
+            else:
+                close = pend >= limit
+            if l > 0 and not close:
                 continue
             plan.append((l, top))
-            top, pend = l - 1, 0
+            top, pend, n_in, si = l - 1, 0, 0, si + 1
         return plan
 
     def heap_bytes(self, world: int = 8) -> int:
@@ -78,7 +85,8 @@ class MLPConfig:
         biggest = max(self.sizes[l] * self.sizes[l + 1] for l in range(self.nlayers))
         # a bucket closes once it holds >= bucket_mb, so it is smaller than bucket_mb + the biggest layer
         bucket = int(self.resolved_bucket_mb(world) * (1 << 20) / 4)
-        frames = (min(p, bucket + biggest) + 1023) // 512 + (biggest + 511) // 512
+        largest = max(sum(self.sizes[l] * self.sizes[l + 1] + 1024 for l in range(lo, hi + 1)) for lo, hi in self.bucket_plan(world))
+        frames = (min(p, max(bucket + biggest, largest)) + 1023) // 512 + (biggest + 511) // 512
         # fp32 weights + fp32 gradients, two compressed-gradient buffers per layer (GEMM epilogue output),
         # the communicator's staging for the largest bucket, slack for alignment
         return p * 8 + p * 3 + frames * (2 * 1024 + 2 * 2048) + (8 << 20) + self.nlayers * 32768

@@ -81,6 +81,18 @@ def allreduce(grads: torch.Tensor, algo: str = "exact", codec: int = CODEC_F32, 
     return out
 
 
+def bucket_plan(layer_bytes, bucket_bytes: int, schedule=None):
+    """The GPU trainer's gradient-bucket plan (csrc/api/bucket_plan.h), computed by the native code:
+    [(lowest layer, highest layer), ...] in issue order (last layer first)."""
+    import ctypes as C
+    n = len(layer_bytes)
+    lb = (C.c_size_t * n)(*[int(b) for b in layer_bytes])
+    sched = (C.c_int * len(schedule))(*schedule) if schedule else None
+    lo, hi = (C.c_int * n)(), (C.c_int * n)()
+    N.oracle().ainic_ref_bucket_plan(n, lb, int(bucket_bytes), sched, len(schedule) if schedule else 0, lo, hi)
+    return [(lo[l], hi[l]) for l in range(n - 1, -1, -1) if lo[l] == l]
+
+
 def sgd(w: torch.Tensor, g: torch.Tensor, lr: float) -> torch.Tensor:
     w = _f32(w).clone()
     g = _f32(g)

@@ -77,3 +77,32 @@ def test_bucket_plan_and_heap_sizing(monkeypatch):
     p = cfg.param_count()
     assert cfg.heap_bytes(1) >= p * 8 and cfg.heap_bytes(8) > cfg.heap_bytes(1)
     assert MLPConfig(sizes=[2048] * 11, bucket_mb=1e6).heap_bytes(8) > cfg.heap_bytes(8)
+
+
+def test_native_bucket_planner_matches_the_python_mirror(monkeypatch):
+    """csrc/api/bucket_plan.h is what the GPU trainer runs; the CPU library exports it, so the plan the
+    trainer will use is checked here against MLPConfig.bucket_plan for thresholds and explicit schedules."""
+    import random
+    from fpga_ai_nic_b200.ops import oracle as O
+    rng = random.Random(7)
+    monkeypatch.delenv("AINIC_BUCKET_MB", raising=False)
+    for trial in range(200):
+        nl = rng.randint(1, 12)
+        sizes = [rng.choice([64, 128, 256, 512, 1024, 2048]) for _ in range(nl + 1)]
+        layer_bytes = [sizes[l] * sizes[l + 1] * 4 for l in range(nl)]
+        if trial % 2:
+            sched = [rng.randint(1, 5) for _ in range(rng.randint(1, 4))]
+            monkeypatch.setenv("AINIC_BUCKET_LAYERS", ",".join(map(str, sched)))
+            want = MLPConfig(sizes=sizes).bucket_plan(8)
+            got = O.bucket_plan(layer_bytes, 0, sched)
+        else:
+            monkeypatch.delenv("AINIC_BUCKET_LAYERS", raising=False)
+            mb = rng.choice([0.0, 0.01, 0.5, 3.0, 20.0, 1e6])
+            want = MLPConfig(sizes=sizes, bucket_mb=mb).bucket_plan(8)
+            got = O.bucket_plan(layer_bytes, int(mb * (1 << 20)), None)
+        assert got == want, (sizes, got, want)
+        covered = [l for lo, hi in got for l in range(hi, lo - 1, -1)]
+        assert covered == list(range(nl - 1, -1, -1))
+    monkeypatch.setenv("AINIC_BUCKET_LAYERS", "4,3,2,1")
+    assert MLPConfig.reference().bucket_plan(8) == [(6, 9), (3, 5), (1, 2), (0, 0)]
+    assert O.bucket_plan([16 << 20] * 10, 0, [4, 3, 2, 1]) == [(6, 9), (3, 5), (1, 2), (0, 0)]
