@@ -41,6 +41,11 @@ struct Shared {
   double seconds = 0, t_fwd = 0, t_loss = 0, t_bwd = 0, t_first_bwd = 0;
   float final_loss = 0;
   double checksum = 0;
+  // CHECK=1 (the reference parses the variable but only prints it, :227-228; its per-layer L1-norm check
+  // via libxsmm_matdiff sits inside #if 0, :818-826): per-layer L1 norm and a bit hash of every rank's weights
+  bool check = false;
+  std::vector<std::vector<double>> l1;          // [rank][layer]
+  std::vector<std::vector<uint64_t>> hash;      // [rank][layer]
 };
 
 static int codec_id(const std::string& s) {
@@ -137,6 +142,21 @@ static void rank_main(mmpi_world_t* world, int rank, void* user) {
   }
   mmpi_barrier(world, rank);
   const double t1 = mmpi_wtime();
+  if (S.check) {
+    for (int l = 0; l < L; ++l) {
+      double n1 = 0;
+      uint64_t h = 1469598103934665603ull;   // FNV-1a over the weight bits
+      for (float v : W[l]) {
+        n1 += fabs((double)v);
+        uint32_t u;
+        memcpy(&u, &v, 4);
+        h = (h ^ u) * 1099511628211ull;
+      }
+      S.l1[rank][l] = n1;
+      S.hash[rank][l] = h;
+    }
+    mmpi_barrier(world, rank);
+  }
   if (rank == 0) {
     S.seconds = t1 - t0;
     S.t_fwd = t_fwd; S.t_loss = t_loss; S.t_bwd = t_bwd; S.t_first_bwd = t_first;
@@ -154,7 +174,8 @@ int main(int argc, char** argv) {
   if (argc > 1 && !strcmp(argv[1], "-h")) {
     printf("Usage: %s iters MB fuse_type type bn bk bc C1 C2 ... CN\n", argv[0]);
     printf("  type: A (NIC all-reduce, overlapped), B (MPI_Iallreduce + SGD), F (forward only); fuse_type 0-3\n");
-    printf("  env: AINIC_RANKS (2), AINIC_CODEC (bfp|f32|mxfp8|bf16), AINIC_ALGO (auto|oneshot|twoshot|ring), AINIC_LR (0.1)\n");
+    printf("  env: AINIC_RANKS (2), AINIC_CODEC (bfp|f32|mxfp8|bf16), AINIC_ALGO (auto|oneshot|twoshot|ring), AINIC_LR (0.1),\n");
+    printf("       CHECK=1 (per-layer L1 norms and a bit comparison of every rank's weights after the run)\n");
     return 0;
   }
   int i = 1;
@@ -179,6 +200,9 @@ int main(int argc, char** argv) {
   const int L = (int)c.C.size() - 1;
   printf("MLP: iters %d, global MB %d (%d ranks x %d), fuse %d, type %c, blocking %d/%d/%d (ignored), layers %d\n", c.iters,
          c.global_mb, c.nranks, c.global_mb / c.nranks, c.fuse, c.type, c.bn, c.bk, c.bc, L);
+  if (const char* e = getenv("CHECK")) S.check = atoi(e) != 0;
+  S.l1.assign(c.nranks, std::vector<double>(L, 0.0));
+  S.hash.assign(c.nranks, std::vector<uint64_t>(L, 0));
   S.nics.resize(c.nranks);
   for (int r = 0; r < c.nranks; ++r)
     if (ainic_nic_open(&S.nics[r], nullptr, 1, r, c.nranks)) return 2;
@@ -199,6 +223,16 @@ int main(int argc, char** argv) {
   printf("Bwdupd compute time overlaped = %.5g\n", (S.t_bwd - S.t_first_bwd) / c.iters);
   printf("samples/s = %.5g\n", (double)c.global_mb * c.iters / S.seconds);
   printf("loss = %.6f  weight checksum = %.9g\n", S.final_loss, S.checksum);
+  if (S.check) {
+    bool all_same = true;
+    for (int l = 0; l < L; ++l) {
+      bool same = true;
+      for (int r = 1; r < c.nranks; ++r) same = same && S.hash[r][l] == S.hash[0][l];
+      all_same = all_same && same;
+      printf("CHECK layer %d: L1 norm of weights = %.9g, replicas %s\n", l, S.l1[0][l], same ? "identical" : "DIFFER");
+    }
+    printf("CHECK: weight replicas %s across %d ranks\n", all_same ? "bit-identical" : "differ", c.nranks);
+  }
   printf("NIC latency (rank 0, ms) = %.3f  stall = %.3f\n", ainic_nic_latency_ns(S.nics[0]) / 1e6, ainic_nic_stall_ns(S.nics[0]) / 1e6);
   for (auto* n : S.nics) ainic_nic_close(n);
   return 0;

@@ -11,6 +11,7 @@
 * ``bn bk bc`` are libxsmm blocking factors: accepted for compatibility, meaningless for tcgen05 tiles.
 * env: AINIC_CODEC (auto|f32|bfp|mxfp8|bf16), AINIC_ALGO (auto|oneshot|twoshot|ring), AINIC_LR (0.1),
   DETAILED_PROFILE=1 (per-phase device times), CHECKPOINT=path (save at the end, resume if present),
+  CHECK=1 (per-layer L1 norm of the weights and a bit comparison of the replicas after the run),
   AINIC_BUCKET_MB (fp32 MiB of gradients per fused call; 0 = one call per layer like the reference),
   AINIC_MLP_GRAPH=0 (direct launches instead of replaying the step as a CUDA graph),
   AINIC_FUSE_COMPRESS=0|1|2 (weight-gradient GEMM epilogue: fp32 / wire-format frames / frames stored
@@ -122,6 +123,24 @@ def main(argv):
             print(f"loss = {float(tr.loss_dev.item()) / mb:.6f}")
         c = tr.comm.counters()
         print(f"NIC latency (ms) = {c['busy_ns'] / 1e6:.3f}  stall = {c['wait_ns'] / 1e6:.3f}  timeouts = {c['timeouts']}")
+    if os.environ.get("CHECK") == "1" and typ != "F":
+        # The reference parses CHECK but only prints it (:227-228); its per-layer L1-norm check sits in
+        # "#if 0" (:818-826).  Here: L1 norm of every layer's weights and a bit comparison of the replicas.
+        same_all = True
+        for l in range(cfg.nlayers):
+            w = tr.buffer("weight", l)
+            n1 = float(w.abs().sum(dtype=torch.float64).item())
+            h = w.contiguous().view(torch.int32).to(torch.int64).sum().reshape(1)   # order-independent bit checksum
+            same = True
+            if world > 1:
+                hs = [torch.empty_like(h) for _ in range(world)]
+                dist.all_gather(hs, h)
+                same = all(int(v.item()) == int(hs[0].item()) for v in hs)
+            same_all = same_all and same
+            if rank == 0:
+                print(f"CHECK layer {l}: L1 norm of weights = {n1:.9g}, replicas {'identical' if same else 'DIFFER'}")
+        if rank == 0:
+            print(f"CHECK: weight replicas {'bit-identical' if same_all else 'differ'} across {world} ranks")
     if ck and rank == 0:
         checkpoint.save(tr, ck, step=start + iters)
     if world > 1:

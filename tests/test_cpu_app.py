@@ -59,3 +59,16 @@ def test_forward_only_and_usage(app):
     out = _run(app, [2, 32, 1, "F", 64, 64, 64, 64, 64])
     assert "PERFDUMP" in out
     assert "Usage" in _run(app, ["-h"])
+
+
+def test_check_mode_reports_replica_state(app):
+    """CHECK=1: two-shot keeps the replicas bit-identical; the reference-faithful ring lets the owner of a
+    slice keep the unquantised sum while everybody else decodes BFP, so replicas differ."""
+    args = [3, 96, 0, "A", 32, 32, 32, 128, 256, 128]
+    out = _run(app, args, AINIC_RANKS="3", AINIC_ALGO="twoshot", CHECK="1")
+    assert "CHECK: weight replicas bit-identical across 3 ranks" in out
+    assert len(re.findall(r"^CHECK layer \d+: L1 norm of weights = [0-9.e+-]+, replicas identical$", out, re.M)) == 2
+    out = _run(app, args, AINIC_RANKS="3", AINIC_ALGO="ring", CHECK="1")
+    assert "CHECK: weight replicas differ across 3 ranks" in out
+    out = _run(app, args, AINIC_RANKS="3", AINIC_ALGO="ring", AINIC_CODEC="f32", CHECK="1")
+    assert "CHECK: weight replicas bit-identical across 3 ranks" in out
