@@ -46,7 +46,9 @@ struct EpiParams {
 };
 
 // Output selector of the epilogue.
-constexpr int OUT_BF16 = 0, OUT_FP32 = 1, OUT_COMPRESSED = 2;
+// OUT_COMPRESSED_STAGED: same bytes as OUT_COMPRESSED, written through shared memory (epilogue_store_frames);
+// a separate instantiation so that the direct variant keeps its register count and shared-memory size.
+constexpr int OUT_BF16 = 0, OUT_FP32 = 1, OUT_COMPRESSED = 2, OUT_COMPRESSED_STAGED = 3;
 
 // 32 fp32 values of one row -> two BFP16x8 blocks: w[0..7] = int8 mantissas, return = the two shared
 // exponents (low byte first).  Same bits as bfp_exp_field / bfp_quant value by value; the rounding mode

@@ -29,7 +29,7 @@ __host__ __device__ constexpr int num_stages(int block_n) {
 // Compressed output of tiles whose rows never straddle a frame is staged through shared memory
 // (epilogue_store_frames): 32 * block_n bytes for each of the four epilogue warps.
 __host__ __device__ constexpr bool staged_frames(int block_n, int out) {
-  return out == OUT_COMPRESSED && 512 % block_n == 0 && block_n >= 128;
+  return out == OUT_COMPRESSED_STAGED && 512 % block_n == 0 && block_n >= 128;
 }
 __host__ __device__ constexpr int staging_bytes(int block_n, int out) { return staged_frames(block_n, out) ? 4 * 32 * block_n : 0; }
 __host__ __device__ constexpr uint32_t tmem_cols(int block_n) {
@@ -159,11 +159,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N);
       if constexpr (staged_frames(BLOCK_N, OUT_F32)) {
-        if (epi_warps == 4 && ep.stage_frames) {   // compressed frames leave through shared memory, whole row segments at a time
+        if (epi_warps == 4) {   // compressed frames leave through shared memory, whole row segments at a time
           uint8_t* stage = smem + kStages * (kABytes + kBBytes) + 256 + (warp - 2) * (32 * BLOCK_N);
           epilogue_store_frames<BLOCK_N>(ep, taddr, m0 + quarter * 32, n0, stage, lane);
         } else {
-          epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
+          epilogue_store<BLOCK_N, OUT_COMPRESSED>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
         }
       } else {
         epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
@@ -280,9 +280,10 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
   }
   // Staging through shared memory pays for itself when the stores cross NVLink (scatter).  For local
   // frames it is opt-in (AINIC_GEMM_STAGE_FRAMES=1): alone on the GPU it is as fast as the direct path
-  // (24.6 vs 25.6 us on the reference layer), inside the training step it is slower (2 ranks, same
-  // box, A/B/A/B: 0.680 vs 0.647 ms/step) - 143 registers and 32 KB more shared memory per CTA leave
-  // less room for the all-reduce CTAs that share the SMs.
+  // (24.6 vs 25.6 us on the reference layer), inside the training step it measured slower (2 ranks,
+  // same box, A/B/A/B: 0.680 vs 0.647 ms/step; cause not isolated).  The staged variant is its own
+  // kernel instantiation (143 registers, 32 KB more shared memory), so the direct one stays as small
+  // as it was when the headline numbers were taken.
   {
     static const int stage_env = getenv("AINIC_GEMM_STAGE_FRAMES") ? atoi(getenv("AINIC_GEMM_STAGE_FRAMES")) : -1;
     ep.stage_frames = stage_env >= 0 ? stage_env : (ep.push_n > 1 ? 1 : 0);
@@ -332,6 +333,13 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
         default: return AINIC_ERR_ARG;
       }
     case AINIC_GEMM_TN:  // C = A[K,M]^T . B[K,N], fp32 out (or compressed frames)
+      if (ep.cgrad && ep.stage_frames) {
+        switch (block_n) {   // 192-wide tiles straddle frames: direct stores below
+          DISPATCH_BN(256, true, true, OUT_COMPRESSED_STAGED)
+          DISPATCH_BN(128, true, true, OUT_COMPRESSED_STAGED)
+          default: break;
+        }
+      }
       if (ep.cgrad) {
         switch (block_n) {
           DISPATCH_BN(256, true, true, OUT_COMPRESSED)
