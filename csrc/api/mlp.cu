@@ -86,6 +86,13 @@ struct ainic_mlp {
   bool use_graph = false;
   bool in_capture = false;
   bool events_stale = false;         // the per-layer events were last recorded inside a capture
+  // Flow mode (csrc/comm/flow.cuh): ONE persistent all-reduce launch per step, started with the backward
+  // pass; it takes each layer as soon as that layer's weight-gradient GEMM (and the backward-data GEMM
+  // still reading the layer's bf16 shadow) have bumped the layer's device-side ready counter.
+  bool flow = false;
+  uint32_t* flow_ready = nullptr;    // [nlayers] producers finished this step (zeroed at the start of every backward)
+  uint32_t* flow_tickets = nullptr;  // [2 * nlayers] last-CTA tickets of the dW / dX GEMMs
+  cudaEvent_t bwd_start = nullptr;
   cudaEvent_t step_done = nullptr;   // end of the last graph-replayed step on the caller's stream
   cudaStream_t cap_stream = nullptr; // origin stream of captures (the caller's may be the legacy stream, which cannot capture)
 };
@@ -101,7 +108,8 @@ static int fail(const char* what) {
 
 extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlayers, const int* sizes, int mb, int fuse,
                                 float lr, float loss_weight, int codec, int bfp_mode, int algo) {
-  if (!out || !comm || nlayers < 1 || !sizes || mb < 1) return AINIC_ERR_ARG;
+  // mb is the K extent of the weight-gradient GEMM (TMA rows of 16 bytes: a multiple of 8 bf16 values)
+  if (!out || !comm || nlayers < 1 || !sizes || mb < 8 || mb % 8) return AINIC_ERR_ARG;
   for (int i = 0; i <= nlayers; ++i)
     if (sizes[i] < 8 || sizes[i] % 8) return AINIC_ERR_ARG;
   ainic_mlp* m = new ainic_mlp();
@@ -202,7 +210,24 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
       }
     }
   }
-  TRY(ainic_comm_reserve(comm, max_bucket_count(m)));
+  {
+    // Flow mode: default from 2 ranks (AINIC_FLOW=0/1 overrides; 1 also works on a single rank, where the
+    // persistent kernel degenerates to a per-layer SGD pass that starts as soon as the layer's dW exists).
+    const int n = ainic_comm_size(comm);
+    int want = n >= 2 ? 1 : 0;
+    if (const char* e = getenv("AINIC_FLOW")) want = atoi(e);
+    m->flow = want != 0 && nlayers <= AINIC_FLOW_MAX_CHUNKS && !m->fuse_scatter;
+  }
+  if (m->flow) {
+    TRY(ainic_comm_reserve_flow(comm, total, nlayers));
+    TRY_CUDA(cudaMalloc(&m->flow_ready, (size_t)nlayers * 4));
+    TRY_CUDA(cudaMalloc(&m->flow_tickets, (size_t)nlayers * 8));
+    TRY_CUDA(cudaMemset(m->flow_ready, 0, (size_t)nlayers * 4));
+    TRY_CUDA(cudaMemset(m->flow_tickets, 0, (size_t)nlayers * 8));
+    TRY_CUDA(cudaEventCreateWithFlags(&m->bwd_start, cudaEventDisableTiming));
+  } else {
+    TRY(ainic_comm_reserve(comm, max_bucket_count(m)));
+  }
   // Graph replay is on by default (AINIC_MLP_GRAPH=0 switches it off).  It needs launch arguments that do
   // not change from step to step: the fused all-reduce keeps its call number (the cross-GPU flag value)
   // in device memory for that reason, and the compressed-gradient double buffer is part of the graph key.
@@ -245,6 +270,9 @@ extern "C" int ainic_mlp_destroy(ainic_mlp_t* m) {
   for (auto p : m->act) cudaFree(p);
   for (auto p : m->dact) cudaFree(p);
   cudaFree(m->loss_sum);
+  cudaFree(m->flow_ready);
+  cudaFree(m->flow_tickets);
+  if (m->bwd_start) cudaEventDestroy(m->bwd_start);
   cudaEventDestroy(m->fwd_done);
   cudaEventDestroy(m->step_done);
   cudaStreamDestroy(m->cap_stream);
@@ -373,6 +401,38 @@ static int step_body(ainic_mlp* m, const void* x_bf16, const int32_t* labels, fl
   plan_buckets(m, blo, bhi);
   auto bucket_count = [&](int lo, int hi) { return bucket_values(m, lo, hi); };
   const int nranks = ainic_comm_size(m->comm), rank = ainic_comm_rank(m->comm);
+  if (m->flow) {
+    // One persistent all-reduce for the whole backward pass, launched BEFORE the GEMMs that feed it: it
+    // sits beside the GEMM CTAs (256 threads, no shared memory) and picks up layer after layer as their
+    // ready counters fill.  The counters are cleared first; every producer of this step is ordered
+    // after that memset (dy_ready events / stream order), the kernel itself through bwd_start.
+    TRY_CUDA(cudaMemsetAsync(m->flow_ready, 0, (size_t)Ln * 4, s));
+    TRY_CUDA(cudaEventRecord(m->bwd_start, s));
+    TRY_CUDA(cudaStreamWaitEvent(m->comm_stream, m->bwd_start, 0));
+    ainic_flow_chunk_t chunks[AINIC_FLOW_MAX_CHUNKS];
+    size_t total = 0;
+    for (int l = 0; l < Ln; ++l) total += m->layers[l].slot;
+    for (int l = Ln - 1, k = 0; l >= 0; --l, ++k) {
+      const Layer& L = m->layers[l];
+      chunks[k].offset = (size_t)(L.g - m->g_arena);
+      chunks[k].count = (((size_t)L.in * L.out) + 511) & ~(size_t)511;
+      chunks[k].ready_index = l;
+      chunks[k].ready_need = l > 0 ? 2 : 1;   // dW_l, and dX_l which reads the shadow this call rewrites
+    }
+    ainic_allreduce_args_t a{};
+    a.grad = m->g_arena;
+    a.weight = m->w_arena;
+    a.weight_bf16 = m->wb_arena;
+    a.count = total;
+    a.lr = m->lr;
+    a.codec = m->codec;
+    a.bfp_mode = m->bfp_mode;
+    a.max_ctas = m->comm_ctas;
+    a.grad_compressed = m->fuse_compress ? m->cg_arena[m->step_idx & 1] : nullptr;
+    TRY(ainic_allreduce_flow(m->comm, &a, chunks, Ln, m->flow_ready, m->comm_stream));
+    m->launches++;
+    for (int k = 0; k < Ln; ++k) TRY_CUDA(cudaEventRecord(m->layers[k].updated, m->comm_stream));
+  }
   for (int l = Ln - 1; l >= 0; --l) {
     Layer& L = m->layers[l];
     // dact[l+1] is final here (for ReLU layers the mask was already applied by the producer below)
@@ -381,6 +441,10 @@ static int step_body(ainic_mlp* m, const void* x_bf16, const int32_t* labels, fl
     TRY_CUDA(cudaStreamWaitEvent(m->wgrad_stream, L.dy_ready, 0));
     ainic_gemm_epilogue_t we{};
     we.alpha = 1.0f;
+    if (m->flow) {
+      we.done_flag = m->flow_ready + l;
+      we.done_ticket = m->flow_tickets + 2 * l;
+    }
     uint8_t* cg = L.cg[m->step_idx & 1];   // null unless the epilogue emits the wire format
     ainic_gemm_scatter_t sc{};
     if (cg) {
@@ -413,13 +477,17 @@ static int step_body(ainic_mlp* m, const void* x_bf16, const int32_t* labels, fl
       ainic_gemm_epilogue_t de{};
       de.alpha = 1.0f;
       de.mask_in = relu ? m->layers[l - 1].mask : nullptr;
+      if (m->flow) {
+        de.done_flag = m->flow_ready + l;
+        de.done_ticket = m->flow_tickets + 2 * l + 1;
+      }
       TRY(ainic_gemm_bf16(AINIC_GEMM_NN, m->dact[l + 1], L.out, L.wb, L.in, m->dact[l], L.in, m->mb, L.in, L.out, &de, 0,
                           m->gemm_ctas, s));
       m->launches++;
       TRY_CUDA(cudaEventRecord(L.dx_done, s));
     }
     // --- fused all-reduce + SGD on the comm stream, once the bucket that ends at layer l is full
-    if (blo[l] != l) continue;
+    if (m->flow || blo[l] != l) continue;
     const int lo = l, hi = bhi[l];                      // bucket = layers lo .. hi, contiguous in the arenas
     TRY_CUDA(cudaStreamWaitEvent(m->comm_stream, L.dw_ready, 0));   // wgrad stream is in order: covers lo .. hi
     // the shadows of lo .. hi are rewritten below; the last backward-data GEMM that reads one of them
@@ -446,6 +514,7 @@ static int step_body(ainic_mlp* m, const void* x_bf16, const int32_t* labels, fl
     // join the forked streams: the graph ends when the last update has landed (every weight-gradient
     // GEMM precedes a dw_ready that some bucket's all-reduce waited for)
     for (auto& L : m->layers) TRY_CUDA(cudaStreamWaitEvent(s, L.updated, 0));
+    if (m->flow) TRY_CUDA(cudaStreamWaitEvent(s, m->layers[0].dw_ready, 0));   // the wgrad stream joins here in flow mode
     return AINIC_OK;
   }
   m->first_step = false;

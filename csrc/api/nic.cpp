@@ -271,7 +271,11 @@ static int post(ainic_nic* nic, float* buf, float* weight, int flags, size_t cou
     if (inplace && a.codec == AINIC_CODEC_F32 && nic->nranks > 1) a.algo = AINIC_ALGO_TWOSHOT;
     ainic_comm_set_done_slot_(nic->comm, nic->done_dev + slot * 16);
     int rc = ainic_allreduce_fused(nic->comm, &a, stream);
-    if (rc) { nic->done[slot * 16] = 1; return rc; }
+    if (rc) {   // nothing was launched: do not leave the slot armed for somebody else's next launch
+      ainic_comm_set_done_slot_(nic->comm, nullptr);
+      nic->done[slot * 16] = 1;
+      return rc;
+    }
 #else
     return AINIC_ERR_UNSUPPORTED;
 #endif
@@ -301,7 +305,9 @@ extern "C" int ainic_nic_wait(ainic_nic_t* nic, ainic_rqst_t* rq, double timeout
     }
   }
   std::atomic_thread_fence(std::memory_order_acquire);
-  return AINIC_OK;
+  // the device raises 2 instead of 1 when the launch gave up waiting for a peer (spin time-out):
+  // the weights may hold partial sums, the caller must not treat the request as completed
+  return *slot == 2u ? AINIC_ERR_TIMEOUT : AINIC_OK;
 }
 
 extern "C" int ainic_nic_abort(ainic_nic_t* nic) {

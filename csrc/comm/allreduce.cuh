@@ -29,7 +29,8 @@ namespace comm {
 
 constexpr int kMaxRanks = AINIC_MAX_RANKS;
 constexpr int kMaxCtas = 512;
-constexpr int kFlagPhases = 4;          // 0 start, 1 shard published, 2 in-place reads done, 3 ring messages
+constexpr int kFlagPhases = 6;          // 0 start, 1 shard published, 2 in-place reads done, 3 ring messages,
+                                        // 4 / 5 chunk ready / chunk published of the flow kernel (flow.cuh)
 constexpr int kFlagWords = kFlagPhases * kMaxRanks * kMaxCtas;
 constexpr int kCommThreads = 512;          // 16 warps = one 8192-value ring slice per step
 constexpr int kCommThreadsOverlap = 256;   // one-/two-shot/NVLS: small enough to share an SM with a GEMM CTA
@@ -60,6 +61,7 @@ struct RankCtx {
                                  // parity = its low bit; the last CTA stores it back).  Launch arguments are then
                                  // the same for every call, so a captured launch can be replayed (CUDA graphs).
   uint32_t precompressed;        // stage_c already holds this rank's encoded gradient (GEMM epilogue wrote it)
+  uint32_t pf_depth;             // frames of local weights / gradients requested into L2 ahead of their loads (0 = off)
   unsigned long long timeout_ns;
 };
 
@@ -109,7 +111,9 @@ __device__ __forceinline__ void end_call(const RankCtx& c, const WaitStats& ws, 
     if (c.epoch_ptr) *reinterpret_cast<volatile uint32_t*>(c.epoch_ptr) = ws.epoch;
     if (c.done_slot) {
       __threadfence_system();
-      *c.done_slot = 1u;  // 512'd1 into the request's done cache line (hw/all_reduce.sv:1368-1375)
+      // 512'd1 into the request's done cache line (hw/all_reduce.sv:1368-1375); 2 = completed, but some
+      // flag wait of this launch timed out (ainic_nic_wait maps it to AINIC_ERR_TIMEOUT)
+      *c.done_slot = c.counters[CTR_TIMEOUTS] ? 2u : 1u;
     }
   }
 }
@@ -256,38 +260,53 @@ __device__ __forceinline__ void apply_full_w(const RankCtx& c, size_t f, const f
   }
 }
 
+// L2 prefetch of one frame of local fp32 data (weights or gradients); one lane issues it.
+__device__ __forceinline__ void prefetch_frame_f32(const float* base, size_t frame, int lane) {
+  if (lane == 0) ptx::prefetch_l2_bulk(base + frame * kFrameVals, kFrameVals * 4);
+}
+
 // Reduce frames base + j, j = first, first + step, ... < lim over all ranks in rank order and hand
 // each sum to sink(j, acc, w) together with the frame's (already loaded) weights.  Peers are read in
 // batches of PB; batch k + 1 (possibly of the next frame) is requested before batch k is decoded.
 // src(p, j) = where rank p's copy of frame base + j is read from.
 template <int CODEC, int MODE, class Src, class Sink>
-__device__ __forceinline__ void reduce_stream(const RankCtx& c, size_t base, size_t first, size_t step, size_t lim, int lane,
+__device__ __forceinline__ void reduce_stream(const RankCtx& c, size_t base_, size_t first_, size_t step_, size_t lim_, int lane,
                                               Src src, Sink sink) {
   using FC = FrameCodec<CODEC, MODE>;
   using Raw = typename FC::Raw;
   constexpr int PB = sizeof(Raw) > 32 ? 2 : 4;
+  // frame indices fit 32 bits (2^32 frames = 8 TiB of fp32): half the index registers of size_t
+  const uint32_t base = (uint32_t)base_, first = (uint32_t)first_, step = (uint32_t)step_, lim = (uint32_t)lim_;
   const int N = c.nranks;
   const int nb = (N + PB - 1) / PB;
   if (first >= lim) return;
   Raw cur[PB], nxt[PB];
-  size_t j = first;
+  uint32_t j = first;
   int b = 0;
+  // the weight frames (HBM, ~1 us away) are pulled into L2 pf frames ahead of their loads
+  const uint32_t pf = c.weight ? c.pf_depth * step : 0;   // prefetch distance in frames of this warp's sequence
+  for (uint32_t d = first; pf && d < lim && d - first < pf; d += step) prefetch_frame_f32(c.weight, base + d, lane);
 #pragma unroll
   for (int k = 0; k < PB; ++k)
     if (k < N) FC::load(src(k, j), cur[k], lane);
   float acc[16], w[16], v[16];
 #pragma unroll 1
   for (;;) {
-    size_t nj = j;
+    uint32_t nj = j;
     int nbq = b + 1;
     if (nbq == nb) { nbq = 0; nj = j + step; }
     const bool more = nj < lim;
+    if (b == 0 && pf && j + pf < lim) {
+      prefetch_frame_f32(c.weight, base + j + pf, lane);
+      // uncompressed input: this rank's own copy of the frame is local HBM as well
+      if (CODEC == 0 && lane == 1) ptx::prefetch_l2_bulk(src(c.rank, j + pf), 2048);
+    }
     if (more) {
 #pragma unroll
       for (int k = 0; k < PB; ++k)
         if (nbq * PB + k < N) FC::load(src(nbq * PB + k, nj), nxt[k], lane);
     }
-    if (b == 0 && c.weight) frame_load_f32(c.weight + (base + j) * kFrameVals, kFrameVals, w, lane);
+    if (b == 0 && c.weight) frame_load_f32(c.weight + (size_t)(base + j) * kFrameVals, kFrameVals, w, lane);
 #pragma unroll
     for (int k = 0; k < PB; ++k)
       if (b * PB + k < N) {  // warp-uniform
@@ -306,33 +325,46 @@ __device__ __forceinline__ void reduce_stream(const RankCtx& c, size_t base, siz
 
 // Two-shot gather: apply every other rank's published (reduced) shard.  A warp's (peer, frame) items
 // form one flat sequence; they are fetched G at a time, group k + 1 while group k is applied, and
-// the weights of item i + 1 are requested before item i is decoded.
+// the weights of item i + 1 are requested before item i is decoded.  A second cursor runs pf_depth
+// items ahead of the loads and asks the L2 for the weight frames (no registers held meanwhile).
+// The shards belong to a chunk of `full` complete frames that starts at bucket frame `frame0`; rank
+// p's published frame j of this chunk sits in its stage D at slot d_off + j (whole bucket: 0, 0).
 template <int CODEC, int MODE>
-__device__ __forceinline__ void gather_stream(const RankCtx& c, size_t shard, size_t full, size_t first, size_t step, int lane) {
+__device__ __forceinline__ void gather_stream(const RankCtx& c, size_t shard_, size_t full_, size_t first_, size_t step_, int lane,
+                                              size_t frame0_ = 0, size_t d_off_ = 0) {
   using FC = FrameCodec<CODEC, MODE>;
   using Raw = typename FC::Raw;
   constexpr int G = sizeof(Raw) > 32 ? 1 : 4;
   constexpr uint32_t kNone = 0xFFFFFFFFu;
+  const uint32_t shard = (uint32_t)shard_, full = (uint32_t)full_, first = (uint32_t)first_, step = (uint32_t)step_;
+  const uint32_t frame0 = (uint32_t)frame0_, d_off = (uint32_t)d_off_;
   const int N = c.nranks;
-  auto lim_of = [&](int d) -> size_t {
-    const size_t lo = (size_t)((c.rank + d) % N) * shard;
-    return full <= lo ? 0 : (full - lo < shard ? full - lo : shard);
+  auto lim_of = [&](int d) -> uint32_t {
+    const uint32_t lo = (uint32_t)((c.rank + d) % N) * shard;
+    return full <= lo ? 0u : (full - lo < shard ? full - lo : shard);
   };
-  int dp = 1;         // peers are visited staggered (rank + 1, rank + 2, ...) so the links are used evenly
-  size_t j = first;
-  while (dp < N && j >= lim_of(dp)) ++dp;
+  // cursor over the item sequence: peers are visited staggered (rank + 1, rank + 2, ...) so the links are used evenly
+  struct Cur { int dp; uint32_t j; };
+  auto advance = [&](Cur& q) { q.j += step; while (q.dp < N && q.j >= lim_of(q.dp)) { ++q.dp; q.j = first; } };
+  auto frame_of = [&](const Cur& q) -> uint32_t { return frame0 + (uint32_t)((c.rank + q.dp) % N) * shard + q.j; };
+  Cur it{1, first};
+  while (it.dp < N && it.j >= lim_of(it.dp)) ++it.dp;
+  Cur ahead = it;
+  const uint32_t pf = c.weight ? c.pf_depth : 0;
+  for (uint32_t d = 0; d < pf && ahead.dp < N; ++d) { prefetch_frame_f32(c.weight, frame_of(ahead), lane); advance(ahead); }
   Raw cur[G], nxt[G];
   uint32_t cf[G], nf[G];
   auto fetch = [&](Raw (&r)[G], uint32_t (&fi)[G]) {
 #pragma unroll
     for (int k = 0; k < G; ++k) {
-      if (dp < N) {
-        const int p = (c.rank + dp) % N;
-        const size_t f = (size_t)p * shard + j;
-        fi[k] = (uint32_t)f;
-        FC::load(CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + f * 2048 : c.stage_d[p] + j * FC::kBytes, r[k], lane);
-        j += step;
-        while (dp < N && j >= lim_of(dp)) { ++dp; j = first; }
+      if (it.dp < N) {
+        const int p = (c.rank + it.dp) % N;
+        const uint32_t f = frame_of(it);
+        fi[k] = f;
+        FC::load(CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + (size_t)f * 2048
+                            : c.stage_d[p] + (size_t)(d_off + it.j) * FC::kBytes, r[k], lane);
+        advance(it);
+        if (pf && ahead.dp < N) { prefetch_frame_f32(c.weight, frame_of(ahead), lane); advance(ahead); }
       } else {
         fi[k] = kNone;
       }
@@ -411,7 +443,14 @@ __device__ void oneshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
   const bool own_tail = full < frames && (int)(full % nctas) == cta && (int)((full / nctas) % wpb) == warp;
   if (CODEC != 0 && !c.precompressed) {
 #pragma unroll 1
-    for (size_t f0 = first; f0 < full; f0 += 2 * step) compress_pair<CODEC, MODE>(c, parity_off, f0, f0 + step, f0 + step < full, lane);
+    for (size_t f0 = first; f0 < full; f0 += 2 * step) {
+      if (c.pf_depth) {   // the fp32 gradient is read exactly once: fetch it into L2 ahead of the loads
+        const size_t fa = f0 + (size_t)c.pf_depth * 2 * step;
+        if (fa < full) prefetch_frame_f32(c.grad, fa, lane);
+        if (fa + step < full) prefetch_frame_f32(c.grad, fa + step, lane);
+      }
+      compress_pair<CODEC, MODE>(c, parity_off, f0, f0 + step, f0 + step < full, lane);
+    }
     if (own_tail) tail_compress<CODEC, MODE>(c, parity_off, full, lane);
   }
   if (N > 1) {
@@ -458,7 +497,14 @@ __device__ void twoshot_body(const RankCtx& c, int cta, int nctas, WaitStats& ws
     for (int s = 0; s < N; ++s) {
       const size_t base = (size_t)s * shard, lim = shard_full(s);
 #pragma unroll 1
-      for (size_t j0 = first; j0 < lim; j0 += 2 * step) compress_pair<CODEC, MODE>(c, parity_off, base + j0, base + j0 + step, j0 + step < lim, lane);
+      for (size_t j0 = first; j0 < lim; j0 += 2 * step) {
+        if (c.pf_depth) {
+          const size_t ja = j0 + (size_t)c.pf_depth * 2 * step;
+          if (ja < lim) prefetch_frame_f32(c.grad, base + ja, lane);
+          if (ja + step < lim) prefetch_frame_f32(c.grad, base + ja + step, lane);
+        }
+        compress_pair<CODEC, MODE>(c, parity_off, base + j0, base + j0 + step, j0 + step < lim, lane);
+      }
     }
     if (own_tail) tail_compress<CODEC, MODE>(c, parity_off, full, lane);
   }
@@ -605,6 +651,8 @@ __device__ __forceinline__ void run_rank(const RankCtx& c, int cta, int nctas) {
   }
 }
 
+// The context is a __grid_constant__ parameter: it stays in the constant bank and its peer tables are
+// indexed there (LDC), instead of being copied to local memory for the dynamic indexing by rank.
 // Ring: 16 warps (one per frame of a slice).  One-/two-shot: 8-warp CTAs capped at 144 registers,
 // i.e. 36 K registers per CTA, which fits beside a persistent GEMM CTA (320 threads x 80 = 25.6 K) on one SM.
 #define AINIC_COMM_RING_ATTR __launch_bounds__(kCommThreads)
@@ -613,11 +661,11 @@ template <int ALGO>
 constexpr int comm_threads() { return ALGO == AINIC_ALGO_RING ? kCommThreads : kCommThreadsOverlap; }
 
 template <int ALGO, int CODEC, int MODE>
-__global__ void AINIC_COMM_RING_ATTR allreduce_kernel(const RankCtx c) {
+__global__ void AINIC_COMM_RING_ATTR allreduce_kernel(const __grid_constant__ RankCtx c) {
   run_rank<ALGO, CODEC, MODE>(c, blockIdx.x, gridDim.x);
 }
 template <int ALGO, int CODEC, int MODE>
-__global__ void AINIC_COMM_OVERLAP_ATTR allreduce_ov_kernel(const RankCtx c) {
+__global__ void AINIC_COMM_OVERLAP_ATTR allreduce_ov_kernel(const __grid_constant__ RankCtx c) {
   run_rank<ALGO, CODEC, MODE>(c, blockIdx.x, gridDim.x);
 }
 template <int ALGO, int CODEC, int MODE>

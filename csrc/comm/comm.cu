@@ -12,6 +12,7 @@
 #include <string>
 
 #include "allreduce.cuh"
+#include "flow.cuh"
 
 using namespace ainic;
 using namespace ainic::comm;
@@ -47,6 +48,11 @@ struct ainic_comm {
 };
 
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+// How many frames ahead of its loads a warp asks the L2 for local weights / gradients (AINIC_PF_DEPTH, 0 = off).
+static uint32_t pf_depth() {
+  static const uint32_t d = getenv("AINIC_PF_DEPTH") ? (uint32_t)atoi(getenv("AINIC_PF_DEPTH")) : 8u;
+  return d > 64 ? 64 : d;
+}
 // The ring inbox holds ceil(frames/(16N)) blocks x (2N-2) slices; rounding the block count up costs
 // at most one block = 14 raw slices of 32 KiB.
 static constexpr size_t kRingSlack = 512 * 1024;
@@ -226,8 +232,7 @@ static int check_ring_limits(int nranks, size_t count, int ctas) {
   return per_cta * (2 * nranks - 2) < 4096 ? AINIC_OK : AINIC_ERR_ARG;
 }
 
-static int ensure_staging(ainic_comm* c, size_t count) {
-  const size_t frames = bfp_frames(count);
+static int ensure_staging_frames(ainic_comm* c, size_t frames) {
   if (frames <= c->stage_frames) return AINIC_OK;
   // Grow-only; every rank sees the same call sequence, so offsets stay symmetric.
   const size_t want = frames;
@@ -239,6 +244,13 @@ static int ensure_staging(ainic_comm* c, size_t count) {
   c->stage_frames = want;
   return AINIC_OK;
 }
+static int ensure_staging(ainic_comm* c, size_t count) { return ensure_staging_frames(c, bfp_frames(count)); }
+// The flow kernel uses one copy of stage C (frames x <= 1024 B) and 1/nranks of the frames plus one
+// rounding frame per chunk in stage D: half the frames (+ chunks) of the generic layout cover both.
+static size_t flow_staging_frames(const ainic_comm* c, size_t count, int nchunks) {
+  const size_t frames = bfp_frames(count);
+  return (frames + 1) / 2 + (size_t)nchunks + 1;
+}
 
 extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_allreduce_args_t* a);
 
@@ -247,6 +259,10 @@ extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_a
 extern "C" int ainic_comm_reserve(ainic_comm_t* c, size_t count) {
   if (!c || count == 0) return AINIC_ERR_ARG;
   return ensure_staging(c, count);
+}
+extern "C" int ainic_comm_reserve_flow(ainic_comm_t* c, size_t count, int nchunks) {
+  if (!c || count == 0 || nchunks < 1) return AINIC_ERR_ARG;
+  return ensure_staging_frames(c, flow_staging_frames(c, count, nchunks));
 }
 
 extern "C" int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args_t* a, void* stream) {
@@ -282,10 +298,14 @@ extern "C" int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args
 
 // Everything of a RankCtx that belongs to the communicator (peer tables, flags, staging, epoch).
 // Consumes one epoch: call exactly once per fused launch, in the same order on every rank.
+static int fill_ctx(ainic_comm_t* c, RankCtx* out, const ainic_allreduce_args_t* a, size_t staging_frames);
 extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_allreduce_args_t* a) {
   if (!c || !out || !a) return AINIC_ERR_ARG;
+  return fill_ctx(c, out, a, bfp_frames(a->count));
+}
+static int fill_ctx(ainic_comm_t* c, RankCtx* out, const ainic_allreduce_args_t* a, size_t staging_frames) {
   if (!c->connected) { set_error("communicator not connected"); return AINIC_ERR_ARG; }
-  int rc = ensure_staging(c, a->count);
+  int rc = ensure_staging_frames(c, staging_frames);
   if (rc) return rc;
   RankCtx& ctx = *out;
   ctx.rank = c->rank;
@@ -311,6 +331,7 @@ extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_a
   ctx.parity = 0;
   ctx.epoch_ptr = c->epoch_dev;
   ctx.timeout_ns = c->timeout_ns;
+  ctx.pf_depth = pf_depth();
   ctx.precompressed = 0;
   if (a->grad_compressed && a->codec != AINIC_CODEC_F32) {
     // The GEMM epilogue already produced this rank's frames: read "stage C" from there.  The caller
@@ -334,11 +355,180 @@ extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_a
 }
 extern "C" void ainic_set_error_(const char* msg) { set_error(msg ? msg : ""); }
 
+// ---------------------------------------------------------------------------------------- flow (chunk-pipelined, persistent)
+typedef void (*FlowFn)(const FlowCtx);
+typedef void (*FlowEmulFn)(const FlowCtx*);
+static FlowFn pick_flow(int codec, int mode) {
+  switch (codec) {
+    case AINIC_CODEC_F32: return allreduce_flow_kernel<0, 0>;
+    case AINIC_CODEC_BFP: return mode == AINIC_BFP_HW_EXACT ? allreduce_flow_kernel<1, 0> : allreduce_flow_kernel<1, 1>;
+    case AINIC_CODEC_MXFP8: return allreduce_flow_kernel<2, 0>;
+    case AINIC_CODEC_BF16: return allreduce_flow_kernel<3, 0>;
+  }
+  return nullptr;
+}
+static FlowEmulFn pick_flow_emul(int codec, int mode) {
+  switch (codec) {
+    case AINIC_CODEC_F32: return allreduce_flow_emul_kernel<0, 0>;
+    case AINIC_CODEC_BFP: return mode == AINIC_BFP_HW_EXACT ? allreduce_flow_emul_kernel<1, 0> : allreduce_flow_emul_kernel<1, 1>;
+    case AINIC_CODEC_MXFP8: return allreduce_flow_emul_kernel<2, 0>;
+    case AINIC_CODEC_BF16: return allreduce_flow_emul_kernel<3, 0>;
+  }
+  return nullptr;
+}
+// Chunk table shared by the real and the emulated entry: frame ranges + stage D slots.
+static int fill_chunks(FlowCtx& fc, int nranks, size_t total, const ainic_flow_chunk_t* chunks, int nchunks) {
+  if (!chunks || nchunks < 1 || nchunks > kMaxChunks) { set_error("flow: 1..32 chunks"); return AINIC_ERR_ARG; }
+  size_t d_off = 0;
+  for (int k = 0; k < nchunks; ++k) {
+    const ainic_flow_chunk_t& ch = chunks[k];
+    if (ch.count == 0 || (ch.offset % kFrameVals) || (ch.count % kFrameVals) || ch.offset + ch.count > total ||
+        ch.ready_index > 32767 || ch.ready_need < 0 || ch.ready_need > 65535) {
+      set_error("flow: chunk offset / count must be multiples of 512 inside the bucket");
+      return AINIC_ERR_ARG;
+    }
+    fc.chunk[k].frame0 = (uint32_t)(ch.offset / kFrameVals);
+    fc.chunk[k].frames = (uint32_t)(ch.count / kFrameVals);
+    fc.chunk[k].d_off = (uint32_t)d_off;
+    fc.chunk[k].ready_idx = (int16_t)(ch.ready_index < 0 ? -1 : ch.ready_index);
+    fc.chunk[k].ready_need = (uint16_t)ch.ready_need;
+    d_off += (fc.chunk[k].frames + nranks - 1) / nranks;
+  }
+  fc.nchunks = nchunks;
+  return AINIC_OK;
+}
+
+extern "C" int ainic_allreduce_flow(ainic_comm_t* c, const ainic_allreduce_args_t* a, const ainic_flow_chunk_t* chunks,
+                                    int nchunks, const uint32_t* local_ready, void* stream) {
+  if (!c || !a || !a->grad || a->count == 0) return AINIC_ERR_ARG;
+  if (!c->connected) { set_error("communicator not connected"); return AINIC_ERR_ARG; }
+  if (((uintptr_t)a->grad & 15) || ((uintptr_t)a->weight & 15) || ((uintptr_t)a->weight_bf16 & 7) || ((uintptr_t)a->grad_out & 15))
+    return AINIC_ERR_ARG;
+  if (a->grad_scattered) { set_error("flow: scattered input is not supported"); return AINIC_ERR_UNSUPPORTED; }
+  FlowFn kern = pick_flow(a->codec, a->bfp_mode);
+  if (!kern) { set_error("unsupported codec"); return AINIC_ERR_UNSUPPORTED; }
+  if (c->nranks > 1 && !ainic_comm_peer_ptr(c, a->grad, 0) && a->codec == AINIC_CODEC_F32) {
+    set_error("fp32 (in-place) all-reduce needs the gradient bucket inside the symmetric heap");
+    return AINIC_ERR_ARG;
+  }
+  FlowCtx fc;
+  memset(&fc, 0, sizeof(fc));
+  int rc = fill_ctx(c, &fc.c, a, flow_staging_frames(c, a->count, nchunks));
+  if (rc) return rc;
+  rc = fill_chunks(fc, c->nranks, a->count, chunks, nchunks);
+  if (rc) return rc;
+  fc.local_ready = local_ready;
+  fc.c.epoch_ptr = c->epoch_dev + 1;   // flow calls count separately: their flag words (phases 4, 5) are their own
+  fc.c.stage_c_half = 0;
+  fc.c.parity = 0;
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+  }
+  int ctas = a->max_ctas > 0 ? a->max_ctas : sms;   // persistent: one CTA per SM, beside a GEMM CTA
+  if (ctas > kMaxCtas) ctas = kMaxCtas;
+  kern<<<ctas, kCommThreadsOverlap, 0, (cudaStream_t)stream>>>(fc);
+  CUDA_TRY(cudaGetLastError());
+  return AINIC_OK;
+}
+
+extern "C" int ainic_allreduce_flow_emulate(int nranks, float* grads, float* weights, void* weights_bf16, float* grads_out,
+                                            size_t count, float lr, int codec, int bfp_mode, const size_t* chunk_counts,
+                                            int nchunks, int ctas_per_rank, void* stream) {
+  if (nranks < 1 || nranks > kMaxRanks || !grads || count == 0 || !chunk_counts) return AINIC_ERR_ARG;
+  if (((uintptr_t)grads & 15) || ((uintptr_t)weights & 15) || ((uintptr_t)grads_out & 15) || ((uintptr_t)weights_bf16 & 7) || (count % kFrameVals)) {
+    set_error("flow emulate: 16-byte aligned buffers and count % 512 == 0");
+    return AINIC_ERR_ARG;
+  }
+  FlowEmulFn kern = pick_flow_emul(codec, bfp_mode);
+  if (!kern) return AINIC_ERR_UNSUPPORTED;
+  ainic_flow_chunk_t chunks[kMaxChunks];
+  if (nchunks < 1 || nchunks > kMaxChunks) return AINIC_ERR_ARG;
+  {
+    size_t off = 0;
+    for (int k = 0; k < nchunks; ++k) off += chunk_counts[k];
+    if (off != count) { set_error("flow emulate: chunk counts must add up to count"); return AINIC_ERR_ARG; }
+    for (int k = 0; k < nchunks; ++k) {   // last chunk first, like the layers of a backward pass
+      off -= chunk_counts[nchunks - 1 - k];
+      chunks[k] = {off, chunk_counts[nchunks - 1 - k], k, 1};
+    }
+  }
+  const int ctas = ctas_per_rank > 0 ? ctas_per_rank : 4;
+  int dev = 0, sms = 0, per_sm = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kCommThreadsOverlap, 0));
+  if ((long)ctas * nranks > (long)sms * per_sm) { set_error("emulation grid exceeds co-resident capacity"); return AINIC_ERR_ARG; }
+  const size_t frames = bfp_frames(count);
+  const size_t c_bytes = align_up(frames * 1024, 256), d_bytes = align_up((frames + (size_t)nchunks * nranks) * 2048, 256);
+  const size_t flag_bytes = kFlagWords * sizeof(uint32_t), ctr_bytes = 256;
+  const size_t per_rank = c_bytes + d_bytes + flag_bytes + ctr_bytes;
+  uint8_t* scratch = nullptr;
+  FlowCtx* d_ctx = nullptr;
+  CUDA_TRY(cudaMalloc(&scratch, per_rank * nranks + 256));
+  if (cudaMalloc(&d_ctx, sizeof(FlowCtx) * nranks) != cudaSuccess) { cudaFree(scratch); return AINIC_ERR_CUDA; }
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(scratch, 0, per_rank * nranks + 256, s);
+  // local ready counters: all producers "finished" (value 1) - the wait path still runs
+  uint32_t* ready = reinterpret_cast<uint32_t*>(scratch + per_rank * nranks);
+  if (e == cudaSuccess) e = cudaMemsetAsync(ready, 1, 256, s);   // every word 0x01010101 >= 1
+  FlowCtx* h = new FlowCtx[nranks];
+  memset(h, 0, sizeof(FlowCtx) * nranks);
+  auto base = [&](int r) { return scratch + (size_t)r * per_rank; };
+  int rc = AINIC_OK;
+  for (int r = 0; r < nranks && rc == AINIC_OK; ++r) {
+    RankCtx& x = h[r].c;
+    x.rank = r;
+    x.nranks = nranks;
+    x.grad = grads + (size_t)r * count;
+    x.weight = weights ? weights + (size_t)r * count : nullptr;
+    x.wshadow = weights_bf16 ? static_cast<__nv_bfloat16*>(weights_bf16) + (size_t)r * count : nullptr;
+    x.grad_out = grads_out ? grads_out + (size_t)r * count : nullptr;
+    for (int p = 0; p < nranks; ++p) {
+      x.peer_grad[p] = grads + (size_t)p * count;
+      x.stage_c[p] = base(p);
+      x.stage_d[p] = base(p) + c_bytes;
+      x.flags[p] = reinterpret_cast<uint32_t*>(base(p) + c_bytes + d_bytes);
+    }
+    x.counters = reinterpret_cast<unsigned long long*>(base(r) + c_bytes + d_bytes + flag_bytes);
+    x.count = count;
+    x.lr = lr;
+    x.epoch = 1;
+    x.timeout_ns = 5ull * 1000 * 1000 * 1000;
+    x.pf_depth = pf_depth();
+    rc = fill_chunks(h[r], nranks, count, chunks, nchunks);
+    h[r].local_ready = ready;
+  }
+  if (rc == AINIC_OK && e == cudaSuccess) e = cudaMemcpyAsync(d_ctx, h, sizeof(FlowCtx) * nranks, cudaMemcpyHostToDevice, s);
+  const FlowCtx* arg0 = d_ctx;
+  void* args[] = {(void*)&arg0};
+  if (rc == AINIC_OK && e == cudaSuccess) e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas, nranks), dim3(kCommThreadsOverlap), args, 0, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  unsigned long long ctr[8] = {};
+  if (rc == AINIC_OK && e == cudaSuccess) cudaMemcpy(ctr, h[0].c.counters, sizeof(ctr), cudaMemcpyDeviceToHost);
+  delete[] h;
+  cudaFree(scratch);
+  cudaFree(d_ctx);
+  if (rc) return rc;
+  if (e != cudaSuccess) { set_error(std::string("flow emulate: ") + cudaGetErrorString(e)); return AINIC_ERR_CUDA; }
+  if (ctr[CTR_TIMEOUTS]) { set_error("flow emulate: flag wait timed out"); return AINIC_ERR_TIMEOUT; }
+  return AINIC_OK;
+}
+
 // ---------------------------------------------------------------------------------------- emulation
 extern "C" int ainic_allreduce_emulate(int nranks, float* grads, float* weights, void* weights_bf16, float* grads_out,
                                        size_t count, float lr, int codec, int bfp_mode, int algo, int ctas_per_rank,
                                        void* stream) {
   if (nranks < 1 || nranks > kMaxRanks || !grads || count == 0) return AINIC_ERR_ARG;
+  // rank r's rows start at base + r * count and are accessed with 128-bit loads / stores
+  if (((uintptr_t)grads & 15) || ((uintptr_t)weights & 15) || ((uintptr_t)grads_out & 15) || ((uintptr_t)weights_bf16 & 7) ||
+      (nranks > 1 && (count & 3))) {
+    set_error("emulate: buffers must be 16-byte aligned and count a multiple of 4 when nranks > 1");
+    return AINIC_ERR_ARG;
+  }
   algo = resolve_algo(algo, nranks, count);
   EmulFn kern = pick_emul(algo, codec, bfp_mode);
   if (!kern) return AINIC_ERR_UNSUPPORTED;
@@ -357,9 +547,18 @@ extern "C" int ainic_allreduce_emulate(int nranks, float* grads, float* weights,
   uint8_t* scratch = nullptr;
   RankCtx* d_ctx = nullptr;
   CUDA_TRY(cudaMalloc(&scratch, per_rank * nranks));
-  CUDA_TRY(cudaMalloc(&d_ctx, sizeof(RankCtx) * nranks));
+  if (cudaMalloc(&d_ctx, sizeof(RankCtx) * nranks) != cudaSuccess) {
+    cudaFree(scratch);
+    set_error("emulate: cudaMalloc of the context table failed");
+    return AINIC_ERR_CUDA;
+  }
   cudaStream_t s = (cudaStream_t)stream;
-  CUDA_TRY(cudaMemsetAsync(scratch, 0, per_rank * nranks, s));
+  if (cudaMemsetAsync(scratch, 0, per_rank * nranks, s) != cudaSuccess) {
+    cudaFree(scratch);
+    cudaFree(d_ctx);
+    set_error("emulate: clearing the scratch failed");
+    return AINIC_ERR_CUDA;
+  }
   RankCtx h[kMaxRanks];
   memset(h, 0, sizeof(h));
   auto base = [&](int r) { return scratch + (size_t)r * per_rank; };
@@ -385,11 +584,12 @@ extern "C" int ainic_allreduce_emulate(int nranks, float* grads, float* weights,
     x.epoch = 1;
     x.parity = 0;
     x.timeout_ns = 5ull * 1000 * 1000 * 1000;
+    x.pf_depth = pf_depth();
   }
-  CUDA_TRY(cudaMemcpyAsync(d_ctx, h, sizeof(RankCtx) * nranks, cudaMemcpyHostToDevice, s));
+  cudaError_t e = cudaMemcpyAsync(d_ctx, h, sizeof(RankCtx) * nranks, cudaMemcpyHostToDevice, s);
   const RankCtx* arg0 = d_ctx;
   void* args[] = {(void*)&arg0};
-  cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas, nranks), dim3(threads_for(algo)), args, 0, s);
+  if (e == cudaSuccess) e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas, nranks), dim3(threads_for(algo)), args, 0, s);
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   unsigned long long ctr[8] = {};
   if (e == cudaSuccess) cudaMemcpy(ctr, h[0].counters, sizeof(ctr), cudaMemcpyDeviceToHost);

@@ -18,14 +18,20 @@
 //
 // Rules for callers:
 //  * The first call on each device looks up the device address of the scratch array
-//    (cudaGetSymbolAddress, with that device current).  Make that first call before any stream
-//    capture starts in the process.
+//    (cudaGetSymbolAddress, with that device current); the very first call in the process also
+//    page-locks a 4 KiB host array the counters are copied into.  Make that first call - with the
+//    algorithm / codec you will use later, so the kernel is loaded - before any stream capture
+//    starts in the process.
 //  * All calls share the one array and it keeps whatever the previous call left in it.  The
 //    entry point re-zeroes the flag words and counters on `stream` before every launch; the
 //    staging bytes need no clearing because every byte that is read was written earlier in the
 //    same call.  Two calls whose GPU work overlaps (different streams, or two host threads) would
 //    trample each other's flags and staging data - serialise them.
-//  * Like ainic_allreduce_emulate() the call returns after the kernel has finished.
+//  * Like ainic_allreduce_emulate() the call returns after the kernel has finished.  All of its
+//    work (flag clearing, the launch, the counter read-back) is asynchronous work on `stream`
+//    followed by one cudaStreamSynchronize(stream); nothing is issued to the legacy default
+//    stream.  If another thread may have a stream capture open, pass a stream created with
+//    cudaStreamNonBlocking (stream 0 would serialise against, and be refused by, that capture).
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
@@ -59,6 +65,12 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[kScratchBytes];
 constexpr int kMaxDevices = 64;
 std::mutex g_setup_mu;
 unsigned char* g_scratch_dev_ptr[kMaxDevices] = {};
+// Host landing area for the counter read-back.  Page-locked once (cudaHostRegister pins existing
+// memory, it allocates nothing) so that the copy is a true asynchronous DMA on the caller's stream;
+// if pinning is refused the copy still works through the driver's pageable path.
+alignas(4096) unsigned long long g_ctr_host[4096 / sizeof(unsigned long long)];
+bool g_ctr_host_tried = false;
+static_assert(sizeof(g_ctr_host) >= sizeof(unsigned long long) * kNaMaxRanks * kNumCounters, "counter landing area");
 
 struct EmulArgs {
   RankCtx ctx[kNaMaxRanks];
@@ -67,11 +79,11 @@ static_assert(sizeof(EmulArgs) <= 4000, "contexts must fit in kernel parameter s
 typedef void (*ByValFnT)(const EmulArgs);
 
 template <int ALGO, int CODEC, int MODE>
-__global__ void AINIC_COMM_RING_ATTR allreduce_emul_byval_kernel(const EmulArgs args) {
+__global__ void AINIC_COMM_RING_ATTR allreduce_emul_byval_kernel(const __grid_constant__ EmulArgs args) {
   run_rank<ALGO, CODEC, MODE>(args.ctx[blockIdx.y], blockIdx.x, gridDim.x);
 }
 template <int ALGO, int CODEC, int MODE>
-__global__ void AINIC_COMM_OVERLAP_ATTR allreduce_emul_byval_ov_kernel(const EmulArgs args) {
+__global__ void AINIC_COMM_OVERLAP_ATTR allreduce_emul_byval_ov_kernel(const __grid_constant__ EmulArgs args) {
   run_rank<ALGO, CODEC, MODE>(args.ctx[blockIdx.y], blockIdx.x, gridDim.x);
 }
 template <int ALGO, int CODEC, int MODE>
@@ -124,6 +136,10 @@ unsigned char* scratch_on_current_device(char* errbuf, size_t n, int* rc) {
       return nullptr;
     }
     g_scratch_dev_ptr[dev] = p;
+  }
+  if (!g_ctr_host_tried) {
+    g_ctr_host_tried = true;
+    if (cudaHostRegister(g_ctr_host, sizeof(g_ctr_host), cudaHostRegisterPortable) != cudaSuccess) cudaGetLastError();
   }
   return g_scratch_dev_ptr[dev];
 }
@@ -200,13 +216,16 @@ extern "C" int ainic_allreduce_emulate_noalloc(int nranks, float* grads, float* 
   }
   void* kargs[] = {(void*)&args};
   cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas, nranks), dim3(algo == AINIC_ALGO_RING ? kCommThreads : kCommThreadsOverlap), kargs, 0, s);
+  // Time-out check: every rank's counter block comes back with an asynchronous copy on the caller's
+  // stream, then ONE stream synchronisation.  Nothing here touches the legacy default stream (a
+  // synchronous cudaMemcpy would, and that is refused while another thread holds a global-mode
+  // stream capture open), so pass a non-blocking stream of your own if captures may be in progress.
+  unsigned long long (*ctr)[kNumCounters] = reinterpret_cast<unsigned long long (*)[kNumCounters]>(g_ctr_host);
+  for (int r = 0; r < nranks && e == cudaSuccess; ++r)
+    e = cudaMemcpyAsync(ctr[r], args.ctx[r].counters, sizeof(ctr[r]), cudaMemcpyDeviceToHost, s);
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   if (e != cudaSuccess) return fail(errbuf, errbuf_len, AINIC_ERR_CUDA, "no-alloc all-reduce: launch failed: %s", cudaGetErrorString(e));
-  unsigned long long ctr[8] = {};
-  for (int r = 0; r < nranks; ++r) {
-    if (cudaMemcpy(ctr, args.ctx[r].counters, sizeof(ctr), cudaMemcpyDeviceToHost) != cudaSuccess)
-      return fail(errbuf, errbuf_len, AINIC_ERR_CUDA, "no-alloc all-reduce: reading counters failed: %s", cudaGetErrorString(cudaGetLastError()));
-    if (ctr[CTR_TIMEOUTS]) return fail(errbuf, errbuf_len, AINIC_ERR_TIMEOUT, "no-alloc all-reduce: a flag wait timed out%s");
-  }
+  for (int r = 0; r < nranks; ++r)
+    if (ctr[r][CTR_TIMEOUTS]) return fail(errbuf, errbuf_len, AINIC_ERR_TIMEOUT, "no-alloc all-reduce: a flag wait timed out%s");
   return AINIC_OK;
 }

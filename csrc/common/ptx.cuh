@@ -252,6 +252,20 @@ __device__ __forceinline__ void st_stream_v4(void* p, uint4 v) {
                : "memory");
 }
 
+// Ask the L2 to fetch `bytes` (multiple of 16) starting at p (16-byte aligned): no register or shared
+// memory is tied up while the line travels from HBM, so a warp can run many frames ahead of its loads.
+__device__ __forceinline__ void prefetch_l2_bulk(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;\n" ::"l"(p), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+
 // ------------------------------------------------------------------ NVLS (multimem)
 // In-switch fp32 sum of the same 16 bytes on every GPU bound to the multicast object.
 __device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const void* mc_ptr) {

@@ -43,6 +43,10 @@ struct EpiParams {
   int push_n, push_rank;   // push_n <= 1: frames go to cgrad
   uint32_t push_shard, push_frame0;
   int stage_frames;        // compressed output leaves through shared memory (epilogue_store_frames)
+  // "ready" doorbell for a consumer kernel that is already running (the flow all-reduce): the last CTA to
+  // finish bumps *done_flag once every tile of this launch has been stored (release, gpu scope)
+  uint32_t* done_flag;
+  uint32_t* done_ticket;
 };
 
 // Output selector of the epilogue.

@@ -176,11 +176,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   }
 
   tc_fence_before();
+  if (ep.done_flag && warp >= 2) __threadfence();   // this thread's output stores, before the CTA-wide barrier
   __syncthreads();
   tc_fence_after();
   if (warp == 1) {
     __syncwarp();
     tmem_dealloc<kTmemCols>(tmem_base);
+  }
+  if (ep.done_flag && threadIdx.x == 0) {
+    // last-CTA ticket: every CTA's stores are fenced before its increment, so whoever observes the flag
+    // (ld.acquire.gpu in flow.cuh, then the peers it notifies) sees the complete output
+    __threadfence();
+    if (atomicAdd(ep.done_ticket, 1u) == gridDim.x - 1) {
+      *ep.done_ticket = 0u;
+      __threadfence();
+      atomicAdd(ep.done_flag, 1u);
+    }
   }
 }
 
@@ -261,6 +272,9 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
     ep.cgrad = static_cast<uint8_t*>(epi->cgrad);
     ep.codec = epi->codec;
     ep.bfp_mode = epi->bfp_mode;
+    ep.done_flag = epi->done_flag;
+    ep.done_ticket = epi->done_ticket;
+    if (ep.done_flag && (!ep.done_ticket || block_n < 0)) return AINIC_ERR_ARG;   // 1-CTA kernels only
     if (const ainic_gemm_scatter_t* sc = epi->scatter) {
       if (sc->nranks < 1 || sc->nranks > AINIC_MAX_RANKS || sc->rank < 0 || sc->rank >= sc->nranks || sc->shard_frames == 0)
         return AINIC_ERR_ARG;
@@ -308,7 +322,7 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
       const double e = wave_eff(M, N, 128, bn, sms) * 0.80;   // 1-CTA main loop is smem-bandwidth bound
       if (e > best * 1.02) { best = e; block_n = bn; }
     }
-    if (allow_2cta && M >= 256 && sms >= 2) {
+    if (allow_2cta && M >= 256 && sms >= 2 && !ep.done_flag) {
       for (int i = 0; i < 2; ++i) {
         const int bn = kk ? cand2_kk[i] : cand2_mn[i];
         const double e = wave_eff(M, N, 256, bn, sms / 2);

@@ -36,7 +36,11 @@ class GemmScatter(C.Structure):
 class GemmEpilogue(C.Structure):
     _fields_ = [("bias", vp), ("mask_out", vp), ("mask_in", vp), ("alpha", C.c_float), ("relu", C.c_int),
                 ("accumulate", C.c_int), ("cgrad", vp), ("codec", C.c_int), ("bfp_mode", C.c_int),
-                ("scatter", C.POINTER(GemmScatter))]
+                ("scatter", C.POINTER(GemmScatter)), ("done_flag", vp), ("done_ticket", vp)]
+
+
+class FlowChunk(C.Structure):
+    _fields_ = [("offset", sz), ("count", sz), ("ready_index", C.c_int), ("ready_need", C.c_int)]
 
 
 class AllreduceArgs(C.Structure):
@@ -51,12 +55,23 @@ class Rqst(C.Structure):
 
 def _ensure_built(name: str) -> Path:
     path = LIBDIR / name
-    if not path.exists() or os.environ.get("AINIC_REBUILD"):
-        from .utils import build
+    # build_*() are no-ops unless a source or header is newer than the library, so a stale .so left in
+    # the tree after an edit to csrc/ is rebuilt instead of being loaded silently.  AINIC_NO_BUILD=1
+    # (deployments without a compiler) trusts whatever is there.
+    if path.exists() and os.environ.get("AINIC_NO_BUILD") == "1":
+        return path
+    from .utils import build
+    force = bool(os.environ.get("AINIC_REBUILD"))
+    try:
         if "oracle" in name:
-            build.build_oracle()
+            build.build_oracle(force=force)
         else:
-            build.build_cuda()
+            build.build_cuda(force=force)
+    except Exception:
+        if not path.exists():
+            raise
+        import warnings
+        warnings.warn(f"could not rebuild {name}; loading the existing (possibly stale) library")
     return path
 
 
@@ -148,6 +163,9 @@ def cuda() -> C.CDLL:
     lib.ainic_comm_counters.argtypes = [vp, c_u64p]
     lib.ainic_allreduce_fused.argtypes = [vp, C.POINTER(AllreduceArgs), vp]
     lib.ainic_allreduce_emulate.argtypes = [C.c_int, vp, vp, vp, vp, sz, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+    lib.ainic_allreduce_flow.argtypes = [vp, C.POINTER(AllreduceArgs), C.POINTER(FlowChunk), C.c_int, vp, vp]
+    lib.ainic_allreduce_flow_emulate.argtypes = [C.c_int, vp, vp, vp, vp, sz, C.c_float, C.c_int, C.c_int, C.POINTER(sz),
+                                                 C.c_int, C.c_int, vp]
     lib.ainic_nvls_supported.restype = C.c_int
     lib.ainic_nvls_stage1.argtypes = [C.POINTER(vp), C.c_int, C.c_int, sz, C.c_char_p]
     lib.ainic_nvls_stage2.argtypes = [vp]

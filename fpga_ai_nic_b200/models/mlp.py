@@ -87,6 +87,9 @@ class MLPConfig:
         bucket = int(self.resolved_bucket_mb(world) * (1 << 20) / 4)
         largest = max(sum(self.sizes[l] * self.sizes[l + 1] + 1024 for l in range(lo, hi + 1)) for lo, hi in self.bucket_plan(world))
         frames = (min(p, max(bucket + biggest, largest)) + 1023) // 512 + (biggest + 511) // 512
+        # flow mode (one persistent all-reduce per step over every layer) stages the whole model, but needs
+        # only half the generic per-frame staging (ainic_comm_reserve_flow)
+        frames = max(frames, ((p + 511) // 512 + 1) // 2 + self.nlayers + 2)
         # fp32 weights + fp32 gradients, two compressed-gradient buffers per layer (GEMM epilogue output),
         # the communicator's staging for the largest bucket, slack for alignment
         return p * 8 + p * 3 + frames * (2 * 1024 + 2 * 2048) + (8 << 20) + self.nlayers * 32768
@@ -257,7 +260,13 @@ class MLPTrainer:
                 "biases": [self.buffer("bias", l).cpu().clone() for l in range(self.cfg.nlayers)]}
 
     def load_state_dict(self, sd: dict) -> None:
-        assert list(sd["sizes"]) == list(self.cfg.sizes)
+        if list(sd["sizes"]) != list(self.cfg.sizes):
+            raise ValueError(f"checkpoint is for layer sizes {list(sd['sizes'])}, trainer has {list(self.cfg.sizes)}")
+        for l in range(self.cfg.nlayers):
+            for name, t in (("weight", sd["weights"][l]), ("bias", sd["biases"][l])):
+                dst = self.buffer(name, l)
+                if tuple(t.shape) != tuple(dst.shape) or t.dtype != dst.dtype:
+                    raise ValueError(f"checkpoint {name}[{l}] is {tuple(t.shape)} {t.dtype}, expected {tuple(dst.shape)} {dst.dtype}")
         self.wait()
         torch.cuda.synchronize()
         for l in range(self.cfg.nlayers):

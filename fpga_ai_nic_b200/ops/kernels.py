@@ -242,3 +242,25 @@ def allreduce_emulate(grads: torch.Tensor, weights: torch.Tensor | None, lr: flo
     N.check(rc, "allreduce_emulate")
     _count()
     return gout, weights, shadow
+
+
+def allreduce_flow_emulate(grads: torch.Tensor, weights: torch.Tensor | None, lr: float, codec: int, chunk_counts,
+                           bfp_mode: int = HW_EXACT, want_shadow: bool = False, want_grads: bool = True,
+                           ctas_per_rank: int = 4):
+    """The chunk-pipelined (flow) all-reduce with N ranks emulated on one GPU.  ``chunk_counts`` cut the
+    bucket into consecutive chunks (multiples of 512 values) that are processed last chunk first, the
+    way a backward pass produces its layers.  Same return values as :func:`allreduce_emulate`."""
+    _chk(grads, torch.float32)
+    nranks, count = grads.shape
+    gout = torch.zeros_like(grads) if want_grads else None
+    shadow = torch.zeros(nranks, count, dtype=torch.bfloat16, device=grads.device) if want_shadow else None
+    if weights is not None:
+        _chk(weights, torch.float32)
+    cc = (N.sz * len(chunk_counts))(*[int(c) for c in chunk_counts])
+    rc = N.cuda().ainic_allreduce_flow_emulate(nranks, grads.data_ptr(), weights.data_ptr() if weights is not None else None,
+                                               shadow.data_ptr() if shadow is not None else None,
+                                               gout.data_ptr() if gout is not None else None, count, lr, codec, bfp_mode,
+                                               cc, len(chunk_counts), ctas_per_rank, N.stream_ptr())
+    N.check(rc, "allreduce_flow_emulate")
+    _count()
+    return gout, weights, shadow

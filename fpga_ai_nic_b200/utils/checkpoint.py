@@ -23,6 +23,7 @@ def save(trainer, path: str, step: int = 0, extra: dict | None = None) -> None:
 
 
 def load(trainer, path: str) -> dict:
-    sd = torch.load(path, map_location="cpu", weights_only=False)
+    # tensors, ints, lists and plain dicts only: no arbitrary unpickling of an untrusted file
+    sd = torch.load(path, map_location="cpu", weights_only=True)
     trainer.load_state_dict(sd)
     return {"step": sd.get("step", 0), "extra": sd.get("extra", {})}

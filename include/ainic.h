@@ -89,6 +89,9 @@ typedef struct ainic_gemm_epilogue {
   int codec;              /* AINIC_CODEC_BFP or AINIC_CODEC_MXFP8 when cgrad is set */
   int bfp_mode;
   const ainic_gemm_scatter_t* scatter; /* nullable; with it cgrad is ignored and the frames go to the owners' inboxes */
+  uint32_t* done_flag;    /* nullable, device: incremented once (release, gpu scope) by the last CTA of the launch after
+                             every output tile has been stored - the "ready" doorbell a flow all-reduce waits on */
+  uint32_t* done_ticket;  /* device scratch word for done_flag (zero before the first launch; the kernel resets it) */
 } ainic_gemm_epilogue_t;
 /* bf16 operands, fp32 accumulation on tcgen05 tensor cores.  block_n = 0 picks the tile width,
  * max_ctas = 0 uses every SM (a smaller value leaves SMs for a concurrent all-reduce kernel). */
@@ -142,9 +145,35 @@ typedef struct ainic_allreduce_args {
 } ainic_allreduce_args_t;
 /* Fused compress -> (peer pull) -> fp32 reduce -> decompress -> SGD, one kernel launch on stream. */
 int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args_t* args, void* stream);
+/* Flow all-reduce (csrc/comm/flow.cuh): one persistent launch that walks the bucket chunk by chunk - each
+ * chunk goes through compress -> reduce own 1/N -> publish -> gather as soon as its producers have
+ * bumped the chunk's device-side ready counter (ainic_gemm_epilogue_t.done_flag), the flag round
+ * trips of chunk k hidden behind the data movement of chunk k - 1.  In the trainer a chunk is a
+ * layer, launched once per step at the start of the backward pass.  The reference's host posts one
+ * request per layer and keeps two in flight (sw/mlp_mpi_example_f32.cpp:735-788); this is that
+ * pipeline with the doorbell moved into the producer kernel.  Chunks are processed in array order;
+ * offset and count are in values, multiples of 512; args->grad / weight / weight_bf16 /
+ * grad_compressed are the bucket bases and args->count its total extent.  local_ready (device,
+ * nullable) must be zeroed by the caller before this call's producers are launched. */
+#define AINIC_FLOW_MAX_CHUNKS 32
+typedef struct ainic_flow_chunk {
+  size_t offset, count;  /* values from the bucket base; multiples of 512 */
+  int ready_index;       /* index into local_ready, or -1: complete when the call is launched */
+  int ready_need;        /* producers that must have finished (counter value to wait for); 0 means 1 */
+} ainic_flow_chunk_t;
+int ainic_allreduce_flow(ainic_comm_t* c, const ainic_allreduce_args_t* args, const ainic_flow_chunk_t* chunks, int nchunks,
+                         const uint32_t* local_ready, void* stream);
+/* Single-GPU emulation of the flow all-reduce (all ranks' buffers on one device, one cooperative
+ * launch): chunk_counts[nchunks] cut [0, count) into consecutive chunks, processed last chunk first
+ * like the layers of a backward pass. */
+int ainic_allreduce_flow_emulate(int nranks, float* grads, float* weights, void* weights_bf16, float* grads_out, size_t count,
+                                 float lr, int codec, int bfp_mode, const size_t* chunk_counts, int nchunks,
+                                 int ctas_per_rank, void* stream);
 /* Pre-size the communicator's staging for calls of up to `count` values (collective: same call on
  * every rank).  Optional - staging also grows on demand, but growth abandons the old area. */
 int ainic_comm_reserve(ainic_comm_t* c, size_t count);
+/* Same for ainic_allreduce_flow calls of up to `count` values in `nchunks` chunks (needs about half the staging). */
+int ainic_comm_reserve_flow(ainic_comm_t* c, size_t count, int nchunks);
 /* Device-side phase counters of the last completed fused all-reduce (ns from %globaltimer):
  * [0] total busy, [1] waiting for peers, [2] launches.  The analogue of lpbk_latency /
  * stall_* (hw/all_reduce.sv:92-98, :892-1072). */

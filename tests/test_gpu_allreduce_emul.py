@@ -70,3 +70,27 @@ def test_bfp_accuracy_better_than_reference(K, nranks):
     ref_err = max(((ring[r] - exact).norm() / exact.norm()).item() for r in range(nranks))
     assert ours.item() < ref_err
     assert ours.item() < 0.03
+
+
+FLOW_CASES = [(O.CODEC_F32, 0), (O.CODEC_BFP, O.HW_EXACT), (O.CODEC_BFP, O.CLEAN), (O.CODEC_MXFP8, 0), (O.CODEC_BF16, 0)]
+
+
+@pytest.mark.parametrize("codec,mode", FLOW_CASES)
+@pytest.mark.parametrize("nranks", [1, 2, 3, 4, 8])
+@pytest.mark.parametrize("chunks", [[512 * 40], [512 * 7, 512 * 33, 512 * 1, 512 * 16], [512 * 64] * 6])
+def test_flow_allreduce_bit_exact(K, codec, mode, nranks, chunks):
+    """The chunk-pipelined persistent kernel (csrc/comm/flow.cuh) must produce the bits of the two-shot
+    golden model whatever the chunking: the fp32 sum is in rank order and the codec blocks do not
+    depend on which rank owns a frame."""
+    count = sum(chunks)
+    g = _grads(nranks, count, seed=nranks + len(chunks))
+    w0 = _grads(nranks, count, seed=98)[0].repeat(nranks, 1) * 50
+    want = O.allreduce(g, "twoshot", codec, mode)
+    gout, wout, shadow = K.allreduce_flow_emulate(g.cuda(), w0.clone().cuda(), 0.1, codec, chunks, mode, want_shadow=True,
+                                                  ctas_per_rank=3)
+    torch.cuda.synchronize()
+    assert torch.equal(_bits(gout.cpu()), _bits(want)), (gout.cpu() - want).abs().max()
+    for r in range(nranks):
+        w_want = O.sgd(w0[r], want[r], 0.1)
+        assert torch.equal(wout[r].cpu(), w_want)
+        assert torch.equal(shadow[r].cpu(), w_want.to(torch.bfloat16))

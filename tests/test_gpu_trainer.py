@@ -187,3 +187,39 @@ def test_graph_replay_same_bits_as_direct_launches(monkeypatch):
     assert out["0"][1] == pytest.approx(out["1"][1], rel=1e-5)
     for a, b in zip(out["0"][0], out["1"][0]):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("graph", ["0", "1"])
+@pytest.mark.parametrize("fuse", [0, 3])
+def test_flow_mode_same_bits_as_per_layer_calls(monkeypatch, graph, fuse):
+    """Flow mode (one persistent all-reduce per step, layers picked up as the GEMM epilogues ring their
+    device-side doorbells) against one fused call per layer: same weights bit for bit, no flag wait
+    timed out.  On one rank this exercises exactly the producer -> consumer interlock: the persistent
+    kernel is launched BEFORE the GEMMs that feed it."""
+    from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer
+    from fpga_ai_nic_b200.ops import kernels as K
+    monkeypatch.setenv("AINIC_TIMEOUT_MS", "3000")
+    monkeypatch.setenv("AINIC_MLP_GRAPH", graph)
+    sizes = [256, 384, 264, 256, 128]
+    cfg = MLPConfig(sizes=sizes, mb=256, fuse=fuse, lr=0.5, loss_weight=1.0, bucket_mb=0.0)
+    g = torch.Generator().manual_seed(31)
+    xs = [K.cast_bf16((torch.rand(cfg.mb, sizes[0], generator=g) - 0.5).cuda()) for _ in range(2)]
+    ys = [torch.randint(0, sizes[-1], (cfg.mb,), generator=g, dtype=torch.int32).cuda() for _ in range(2)]
+    out = {}
+    for flow in ("0", "1"):
+        monkeypatch.setenv("AINIC_FLOW", flow)
+        tr = MLPTrainer(cfg)
+        n0 = tr.comm.counters()["launches"]
+        for i in range(5):
+            tr.step(xs[i % 2], ys[i % 2])
+        tr.wait()
+        torch.cuda.synchronize()
+        ctr = tr.check_health()
+        out[flow] = ([tr.buffer("weight", l).cpu().clone() for l in range(cfg.nlayers)],
+                     [tr.buffer("shadow", l).cpu().clone() for l in range(cfg.nlayers)], ctr["launches"] - n0)
+        tr.close()
+    assert out["0"][2] == 5 * cfg.nlayers and out["1"][2] == 5      # one launch per step in flow mode
+    for a, b in zip(out["0"][0], out["1"][0]):
+        assert torch.equal(a, b)
+    for a, b in zip(out["0"][1], out["1"][1]):
+        assert torch.equal(a, b)
