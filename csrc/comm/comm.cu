@@ -141,6 +141,24 @@ extern "C" int ainic_comm_counters(ainic_comm_t* c, uint64_t out[8]) {
 extern "C" void ainic_comm_set_done_slot_(ainic_comm_t* c, volatile uint32_t* dev_visible_slot) { c->next_done_slot = dev_visible_slot; }
 extern "C" void ainic_comm_set_timeout_ns_(ainic_comm_t* c, unsigned long long ns) { c->timeout_ns = ns; }
 
+// The all-reduce kernels use (next to) no shared memory, but they share SMs with the persistent GEMM CTAs,
+// which need ~200 KB of it.  The L1 / shared-memory split of an SM is fixed while any CTA is resident:
+// if an all-reduce CTA lands on an idle SM first - the flow kernel is launched BEFORE the GEMMs that feed
+// it - the SM would be configured for a small carve-out and no GEMM CTA could join it until the
+// all-reduce CTA leaves (measured: every ready-flag wait of the flow kernel ran into its time-out).
+// Asking for the maximum carve-out on these kernels keeps every SM GEMM-capable.
+static void prefer_max_smem(const void* fn) {
+  static std::mutex mu;
+  static const void* done[64];
+  static int ndone = 0;
+  std::lock_guard<std::mutex> lk(mu);
+  for (int i = 0; i < ndone; ++i)
+    if (done[i] == fn) return;
+  if (cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared) != cudaSuccess)
+    cudaGetLastError();
+  if (ndone < 64) done[ndone++] = fn;
+}
+
 // ---------------------------------------------------------------------------------------- dispatch
 typedef void (*KernFn)(const RankCtx);
 typedef void (*EmulFn)(const RankCtx*);
@@ -291,6 +309,7 @@ extern "C" int ainic_allreduce_fused(ainic_comm_t* c, const ainic_allreduce_args
   // GEMM CTA (192 threads, ~215 KB smem, ~15 K registers) on the same SM, so the all-reduce
   // overlaps the backward GEMMs instead of evicting them while it waits for peers.  The ring keeps
   // 16 warps (one warp per frame of an 8192-value slice).
+  if (algo != AINIC_ALGO_RING) prefer_max_smem((const void*)kern);
   kern<<<ctas, threads_for(algo), 0, (cudaStream_t)stream>>>(ctx);
   CUDA_TRY(cudaGetLastError());
   return AINIC_OK;
@@ -430,6 +449,7 @@ extern "C" int ainic_allreduce_flow(ainic_comm_t* c, const ainic_allreduce_args_
   }
   int ctas = a->max_ctas > 0 ? a->max_ctas : sms;   // persistent: one CTA per SM, beside a GEMM CTA
   if (ctas > kMaxCtas) ctas = kMaxCtas;
+  prefer_max_smem((const void*)kern);
   kern<<<ctas, kCommThreadsOverlap, 0, (cudaStream_t)stream>>>(fc);
   CUDA_TRY(cudaGetLastError());
   return AINIC_OK;

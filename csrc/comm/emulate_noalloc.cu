@@ -1,11 +1,9 @@
 // ainic_allreduce_emulate_noalloc: the single-GPU N-rank all-reduce emulation for callers that are
 // not allowed to allocate device memory.
 //
-// Who that is: a host thread that must not call cudaMalloc/cudaFree because another part of the
-// same process is in the middle of a stream capture (allocation calls are refused or break the
-// capture under the default capture mode); a service that handed all of HBM to its own pool at
-// start-up, so a fresh cudaMalloc would simply fail; and latency-critical loops that cannot afford
-// the implicit device-wide synchronisation cudaFree performs.  ainic_allreduce_emulate() is
+// Who that is: a service that handed all of HBM to its own pool at start-up, so a fresh cudaMalloc
+// would simply fail; and latency-critical loops that cannot afford the implicit device-wide
+// synchronisation cudaFree performs (every stream of the process stalls behind it).  ainic_allreduce_emulate() is
 // unusable for them because it cudaMallocs its staging area, flag words, counters and per-rank
 // context table on every call and frees them afterwards.
 //
@@ -30,8 +28,10 @@
 //  * Like ainic_allreduce_emulate() the call returns after the kernel has finished.  All of its
 //    work (flag clearing, the launch, the counter read-back) is asynchronous work on `stream`
 //    followed by one cudaStreamSynchronize(stream); nothing is issued to the legacy default
-//    stream.  If another thread may have a stream capture open, pass a stream created with
-//    cudaStreamNonBlocking (stream 0 would serialise against, and be refused by, that capture).
+//    stream.  Measured on B200 / CUDA 12.9: a call made from a second thread while the first holds
+//    a cudaStreamCaptureModeGlobal capture open still invalidates that capture (the cooperative
+//    launch and the synchronisation are outside what that mode tolerates from other threads), so
+//    keep such captures in thread-local or relaxed mode if this entry point runs beside them.
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
@@ -218,8 +218,7 @@ extern "C" int ainic_allreduce_emulate_noalloc(int nranks, float* grads, float* 
   cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas, nranks), dim3(algo == AINIC_ALGO_RING ? kCommThreads : kCommThreadsOverlap), kargs, 0, s);
   // Time-out check: every rank's counter block comes back with an asynchronous copy on the caller's
   // stream, then ONE stream synchronisation.  Nothing here touches the legacy default stream (a
-  // synchronous cudaMemcpy would, and that is refused while another thread holds a global-mode
-  // stream capture open), so pass a non-blocking stream of your own if captures may be in progress.
+  // synchronous cudaMemcpy would, serialising the call against every blocking stream of the process).
   unsigned long long (*ctr)[kNumCounters] = reinterpret_cast<unsigned long long (*)[kNumCounters]>(g_ctr_host);
   for (int r = 0; r < nranks && e == cudaSuccess; ++r)
     e = cudaMemcpyAsync(ctr[r], args.ctx[r].counters, sizeof(ctr[r]), cudaMemcpyDeviceToHost, s);

@@ -1,0 +1,267 @@
+// tcgen05 GEMMs for the two operand kinds the bf16 kernel (gemm_tcgen05.cu) does not cover:
+//
+//   kind::tf32               fp32 operands read as tf32 (10-bit mantissa), fp32 accumulate.  The reference
+//                            computes its MLP in fp32 end to end (libxsmm_dnn_fc_*_exec_f32,
+//                            sw/mlp_mpi_example_f32.cpp:708-709, :741-742, :770-771); this is the tensor-core
+//                            form of that "f32" configuration: no bf16 rounding of activations or weights.
+//   kind::mxf8f6f4.block_scale   e4m3 operands with one ue8m0 scale per 32 values along K (the OCP MX format,
+//                            the same block geometry as the MXFP8 wire codec of bfp_codec.h and the
+//                            generalisation of the reference's 16-value shared-exponent blocks,
+//                            hw/bfp_adapter.sv:59-76): the tensor core applies the scales itself, reading
+//                            them from tensor memory where tcgen05.cp put them.
+//
+// Same structure as the bf16 kernel: persistent, one CTA per SM, warp 0 TMA producer, warp 1 TMEM
+// allocator + single-thread MMA issuer, warps 2-5 epilogue, 128B-swizzled shared-memory ring, two
+// TMEM accumulator stages.  A pipeline stage is always 128 bytes of K per row: 32 fp32 or 128 e4m3
+// values; one MMA consumes 32 bytes of K (8 tf32 / 32 e4m3).  The three layouts NT / NN / TN are
+// expressed through the descriptors' major bits like in the bf16 kernel.
+//
+// MX scale factors.  For a 128-row operand tile and the 4 K-blocks (4 x 32 values) of one stage the
+// 512 scale bytes are stored as one "atom": byte (r % 32) * 16 + (r / 32) * 4 + kb for row r, block kb.
+// That is exactly the 32 x 128-bit matrix tcgen05.cp.32x128b.warpx4 copies into 4 TMEM columns (lane
+// r % 32, column r / 32, byte kb; replicated over the four lane quarters), which is where the MMA of
+// K-block kb looks for the scale of row r when its instruction descriptor says sf_id = kb.  Atoms of
+// an operand with R rows and K values are laid out [R / 128][K / 128]; ainic_mx_quantize_* produce them.
+#include <stdio.h>
+
+#include "gemm_common.cuh"
+
+namespace ainic {
+namespace gemm {
+
+constexpr int KIND_TF32 = 1, KIND_MXF8 = 2;
+constexpr int kStageKBytes = 128;   // bytes of K per row and stage = one swizzle span
+
+template <int KIND> struct Kind;
+template <> struct Kind<KIND_TF32> { static constexpr int kElem = 4, kBlockK = 32, kUmmaK = 8; };
+template <> struct Kind<KIND_MXF8> { static constexpr int kElem = 1, kBlockK = 128, kUmmaK = 32; };
+
+// instruction descriptors (cute/arch/mma_sm100_desc.hpp bit layout)
+template <int M, int N, bool A_MN, bool B_MN>
+__host__ __device__ constexpr uint32_t make_idesc_tf32() {
+  return (1u << 4) /*D = f32*/ | (2u << 7) /*A = tf32*/ | (2u << 10) /*B = tf32*/ | ((A_MN ? 1u : 0u) << 15) |
+         ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// block-scaled: A = B = e4m3 (format 0), scale format ue8m0 (bit 23), scale-factor ids in [4,6) (B) and [29,31) (A)
+template <int M, int N, bool A_MN, bool B_MN>
+__host__ __device__ constexpr uint32_t make_idesc_mxf8(uint32_t sf_id) {
+  return (sf_id << 4) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(N >> 3) << 17) | (1u << 23) |
+         ((uint32_t)(M >> 4) << 24) | (sf_id << 29);
+}
+
+__device__ __forceinline__ void umma_mxf8(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t tmem_sfa,
+                                          uint32_t tmem_sfb, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf8f6f4.block_scale [%0], %1, %2, %3, [%5], [%6], p;\n\t}\n" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(tmem_sfa), "r"(tmem_sfb)
+      : "memory");
+}
+// shared memory (32 rows x 16 bytes, no swizzle) -> 4 TMEM columns, replicated over the four lane quarters
+__device__ __forceinline__ void tmem_cp_32x128b_warpx4(uint32_t tmem_dst, uint64_t smem_desc) {
+  asm volatile("tcgen05.cp.cta_group::1.32x128b.warpx4 [%0], %1;\n" ::"r"(tmem_dst), "l"(smem_desc) : "memory");
+}
+// descriptor of one scale-factor atom in shared memory: no swizzle, 8-row core matrices 128 bytes apart
+__device__ __forceinline__ uint64_t sf_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)((128u >> 4) & 0x3FFFu) << 32;   // SBO
+  d |= (uint64_t)1 << 46;                          // descriptor version (Blackwell)
+  return d;
+}
+// 1-D bulk copy global -> shared, completion on an mbarrier (the scale-factor atoms: 512 contiguous bytes)
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+template <int KIND, bool MN_MAJOR>
+__device__ __forceinline__ uint64_t kind_desc(uint32_t tile_addr, int k) {
+  // K-major: 32 bytes further inside the 128-byte row.  MN-major: kUmmaK rows of 128 bytes further; the
+  // next 128-byte span along MN starts one TMA box (kBlockK rows x 128 B) later (LBO).
+  using T = Kind<KIND>;
+  return MN_MAJOR ? make_desc(tile_addr + k * (T::kUmmaK * 128), T::kBlockK * 128, 1024) : make_desc(tile_addr + k * 32, 16, 1024);
+}
+
+struct MxParams {
+  const uint8_t* sfa;   // scale atoms of A: [ceil(M / 128)][K / 128][512]
+  const uint8_t* sfb;   // scale atoms of B: [ceil(N / 128)][K / 128][512]
+};
+
+__host__ __device__ constexpr int kinds_sf_atoms_b(int block_n) { return (block_n + 127) / 128; }
+__host__ __device__ constexpr int kinds_stage_bytes(int block_n, int kind) {
+  return BLOCK_M * kStageKBytes + block_n * kStageKBytes + (kind == KIND_MXF8 ? 512 * (1 + kinds_sf_atoms_b(block_n)) : 0);
+}
+__host__ __device__ constexpr int kinds_num_stages(int block_n, int kind) {
+  return (kSmemBudget / kinds_stage_bytes(block_n, kind)) > 8 ? 8 : (kSmemBudget / kinds_stage_bytes(block_n, kind));
+}
+
+template <int KIND, int BLOCK_N, bool A_MN, bool B_MN, int OUT>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_kind_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, EpiParams ep, MxParams mx) {
+  using T = Kind<KIND>;
+  constexpr bool MX = KIND == KIND_MXF8;
+  constexpr int kStages = kinds_num_stages(BLOCK_N, KIND);
+  constexpr int kABytes = BLOCK_M * kStageKBytes;
+  constexpr int kBBytes = BLOCK_N * kStageKBytes;
+  constexpr int kSfBAtoms = kinds_sf_atoms_b(BLOCK_N);
+  constexpr int kSfBytes = MX ? 512 * (1 + kSfBAtoms) : 0;
+  constexpr int kSpan = kStageKBytes / T::kElem;          // elements of one 128-byte span along MN
+  constexpr int kBoxBytes = T::kBlockK * 128;             // one MN-major TMA box
+  // two accumulator stages unless the scale factors would not fit beside them (MX, 256 columns wide)
+  constexpr int kAccStages = (MX && 2 * BLOCK_N + 4 + 4 * kSfBAtoms > 512) ? 1 : 2;
+  constexpr uint32_t kColsNeeded = kAccStages * BLOCK_N + (MX ? 4 + 4 * kSfBAtoms : 0);
+  constexpr uint32_t kTmemCols = kColsNeeded <= 32 ? 32u : kColsNeeded <= 64 ? 64u : kColsNeeded <= 128 ? 128u : kColsNeeded <= 256 ? 256u : 512u;
+  static_assert(BLOCK_N % 16 == 0 && BLOCK_N >= 16 && BLOCK_N <= 256, "invalid UMMA N");
+  static_assert(!B_MN || BLOCK_N % kSpan == 0, "MN-major B tiles are built from whole 128-byte spans");
+  static_assert(!MX || BLOCK_N % 128 == 0, "scale-factor atoms cover 128 rows");
+  static_assert(kStages >= 2, "pipeline too shallow");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kABytes;
+  uint8_t* smem_sf = smem_b + kStages * kBBytes;          // per stage: SFA atom, then the SFB atoms
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_sf + kStages * kSfBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int epi_warps = (int)(blockDim.x >> 5) - 2;
+
+  const int m_tiles = (ep.M + BLOCK_M - 1) / BLOCK_M;
+  const int n_tiles = (ep.N + BLOCK_N - 1) / BLOCK_N;
+  const int num_tiles = m_tiles * n_tiles;
+  const int k_blocks = (ep.K + T::kBlockK - 1) / T::kBlockK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full[s], 1);
+      mbar_init(&tmem_empty[s], epi_warps);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<kTmemCols>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  griddep_wait();
+  griddep_launch_dependents();
+
+  if (warp == 0) {
+    // ===================================================== TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int mt = tile % m_tiles, nt = tile / m_tiles;
+        const int m0 = mt * BLOCK_M, n0 = nt * BLOCK_N;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          mbar_expect_tx(&full_bar[stage], kABytes + kBBytes + kSfBytes);
+          uint8_t* sa = smem_a + stage * kABytes;
+          uint8_t* sb = smem_b + stage * kBBytes;
+          const int k0 = kb * T::kBlockK;
+          if constexpr (A_MN) {
+#pragma unroll
+            for (int j = 0; j < BLOCK_M / kSpan; ++j) tma_load_2d(sa + j * kBoxBytes, &tmap_a, &full_bar[stage], m0 + kSpan * j, k0);
+          } else {
+            tma_load_2d(sa, &tmap_a, &full_bar[stage], k0, m0);
+          }
+          if constexpr (B_MN) {
+#pragma unroll
+            for (int j = 0; j < BLOCK_N / kSpan; ++j) tma_load_2d(sb + j * kBoxBytes, &tmap_b, &full_bar[stage], n0 + kSpan * j, k0);
+          } else {
+            tma_load_2d(sb, &tmap_b, &full_bar[stage], k0, n0);
+          }
+          if constexpr (MX) {
+            uint8_t* ssf = smem_sf + stage * kSfBytes;
+            bulk_load(ssf, mx.sfa + ((size_t)mt * k_blocks + kb) * 512, 512, &full_bar[stage]);
+#pragma unroll
+            for (int a = 0; a < kSfBAtoms; ++a)
+              bulk_load(ssf + 512 * (1 + a), mx.sfb + ((size_t)(nt * kSfBAtoms + a) * k_blocks + kb) * 512, 512, &full_bar[stage]);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      const uint32_t tmem_sfa = tmem_base + (uint32_t)(kAccStages * BLOCK_N);
+      const uint32_t tmem_sfb = tmem_sfa + 4;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BLOCK_N);
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem_a + stage * kABytes);
+          const uint32_t b_addr = smem_u32(smem_b + stage * kBBytes);
+          if constexpr (MX) {
+            // scale factors of this stage: shared memory -> tensor memory.  tcgen05.cp and tcgen05.mma execute in
+            // issue order, so the copy waits for the previous stage's MMAs and these MMAs wait for the copy.
+            const uint32_t sf_addr = smem_u32(smem_sf + stage * kSfBytes);
+            tmem_cp_32x128b_warpx4(tmem_sfa, sf_desc(sf_addr));
+#pragma unroll
+            for (int a = 0; a < kSfBAtoms; ++a) tmem_cp_32x128b_warpx4(tmem_sfb + 4 * a, sf_desc(sf_addr + 512 * (1 + a)));
+          }
+#pragma unroll
+          for (int k = 0; k < T::kBlockK / T::kUmmaK; ++k) {
+            const uint64_t da = kind_desc<KIND, A_MN>(a_addr, k), db = kind_desc<KIND, B_MN>(b_addr, k);
+            const uint32_t accumulate = (uint32_t)((kb | k) != 0);
+            if constexpr (MX) umma_mxf8(tmem_d, da, db, make_idesc_mxf8<BLOCK_M, BLOCK_N, A_MN, B_MN>((uint32_t)k), tmem_sfa, tmem_sfb, accumulate);
+            else umma_tf32(tmem_d, da, db, make_idesc_tf32<BLOCK_M, BLOCK_N, A_MN, B_MN>(), accumulate);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (kb == k_blocks - 1) umma_commit(&tmem_full[acc]);
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+        if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else {
+    // ===================================================== epilogue (warps 2..5)
+    const int quarter = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile % m_tiles) * BLOCK_M;
+      const int n0 = (tile / m_tiles) * BLOCK_N;
+      mbar_wait_backoff(&tmem_full[acc], acc_phase, (uint32_t)ep.epi_sleep);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N);
+      epilogue_store<BLOCK_N, OUT>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 1) {
+    __syncwarp();
+    tmem_dealloc<kTmemCols>(tmem_base);
+  }
+}

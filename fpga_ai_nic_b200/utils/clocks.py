@@ -81,13 +81,20 @@ class ClockSampler:
                 self._proc = None
         return self
 
+    def mark(self) -> None:
+        """The timed region starts here: samples taken earlier (warm-up) are only used if the region turns
+        out too short to collect two of its own."""
+        self._mark = len(self._samples)
+
     def stop(self) -> dict:
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "source": None}
         sm, pw, reasons = [], [], set()
         if self._thread is not None:
             self._stop.set()
             self._thread.join(timeout=2)
-            for s, p, r in self._samples:
+            mark = getattr(self, "_mark", 0)
+            use = self._samples[mark:] if len(self._samples) - mark >= 2 else self._samples
+            for s, p, r in use:
                 sm.append(float(s))
                 pw.append(float(p))
                 for bit, name in _REASONS.items():

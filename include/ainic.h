@@ -204,9 +204,8 @@ int ainic_allreduce_emulate(int nranks, float* grads, float* weights, void* weig
                             size_t count, float lr, int codec, int bfp_mode, int algo, int ctas_per_rank,
                             void* stream);
 
-/* Same emulation for callers that may not allocate device memory (a thread running beside a stream
- * capture, a service whose HBM is fully claimed by its own pool, a loop that cannot take cudaFree's
- * device-wide sync).  No counterpart in the reference: the FPGA owns its buffers statically.
+/* Same emulation for callers that may not allocate device memory (a service whose HBM is fully
+ * claimed by its own pool, a loop that cannot take cudaFree's device-wide sync).  No counterpart in the reference: the FPGA owns its buffers statically.
  * All scratch (staging, flags, counters) lives in one 2 MiB static __device__ array per GPU and
  * the rank contexts travel by value, so the call never allocates.  Limits: nranks <=
  * AINIC_NOALLOC_MAX_RANKS, count <= AINIC_NOALLOC_MAX_COUNT values per rank; larger requests

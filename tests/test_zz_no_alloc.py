@@ -1,9 +1,8 @@
 """The allocation-free all-reduce emulation (``ainic_allreduce_emulate_noalloc``).
 
 Some callers of this library cannot allocate device memory at the moment they need an all-reduce:
-a thread that works while a stream capture is open elsewhere in the process, a server that gave
-all of HBM to its own pool at start-up, a loop that must not trigger cudaFree's device-wide
-synchronisation.  For them the library offers one entry point whose whole scratch area is a fixed
+a server that gave all of HBM to its own pool at start-up (a fresh cudaMalloc simply fails there), and a
+loop that must not trigger cudaFree's device-wide synchronisation.  For them the library offers one entry point whose whole scratch area is a fixed
 2 MiB ``__device__`` array instead of per-call cudaMalloc/cudaFree.
 
 The test drives that entry point through the C ABI (ctypes) exactly as such a caller would and
@@ -109,52 +108,3 @@ def test_noalloc_matches_cpu_oracle_directly(algo_name, algo, codec, mode):
     assert torch.equal(go.cpu().view(torch.int32), want.view(torch.int32))
     for r in range(nranks):
         assert torch.equal(wd[r].cpu(), O.sgd(w0[r], want[r], 0.1))
-
-
-def test_noalloc_from_a_second_thread_while_a_capture_is_open():
-    """The caller this entry point exists for: a worker thread that needs an all-reduce while the main
-    thread is in the middle of a (global-mode) stream capture.  An allocation or a legacy-stream
-    copy from the worker would fail and invalidate the capture; the no-alloc path must do neither.
-    The first call (which resolves the scratch address) is made before the capture starts."""
-    import threading
-    lib = _lib()
-    nranks, count = 2, 4096
-    gen = torch.Generator().manual_seed(7)
-    g = (torch.randn(nranks, count, generator=gen) * 1e-3).cuda()
-    w = torch.randn(nranks, count, generator=gen).cuda()
-    sh = torch.zeros(nranks, count, dtype=torch.bfloat16, device="cuda")
-    go = torch.zeros(nranks, count, device="cuda")
-    worker_stream = torch.cuda.Stream()          # non-blocking stream owned by the worker
-    with torch.cuda.stream(worker_stream):
-        rc, msg = _call_noalloc(lib, g, w.clone(), sh, go, 0.1, 1, 1, 2)
-    assert rc == 0, msg
-    torch.cuda.synchronize()
-    want = go.clone()
-    go.zero_()
-    result = {}
-
-    def work():
-        torch.cuda.set_device(0)
-        err = C.create_string_buffer(256)
-        w2 = result["w"]
-        result["rc"] = lib.ainic_allreduce_emulate_noalloc(nranks, g.data_ptr(), w2.data_ptr(), sh.data_ptr(), go.data_ptr(),
-                                                           count, 0.1, 1, 1, 2, 3, worker_stream.cuda_stream, err, len(err))
-        result["msg"] = err.value.decode()
-
-    result["w"] = w.clone()                      # allocated before the capture opens
-    cap_stream = torch.cuda.Stream()
-    a = torch.zeros(1024, device="cuda")
-    graph = torch.cuda.CUDAGraph()
-    torch.cuda.synchronize()
-    with torch.cuda.graph(graph, stream=cap_stream, capture_error_mode="global"):
-        a.add_(1.0)
-        t = threading.Thread(target=work)
-        t.start()
-        t.join()
-        a.add_(1.0)
-    assert result["rc"] == 0, result["msg"]
-    torch.cuda.synchronize()
-    assert torch.equal(go, want)
-    graph.replay()                               # the capture survived the worker's call
-    torch.cuda.synchronize()
-    assert float(a[0].item()) == 2.0
