@@ -40,6 +40,8 @@ def parse_args():
     ap.add_argument("--codec", default="auto", choices=["auto", "f32", "bfp", "mxfp8", "bf16"])
     ap.add_argument("--algo", default="auto", choices=["auto", "oneshot", "twoshot", "ring"])
     ap.add_argument("--fuse", type=int, default=0)
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"],
+                    help="bf16: bf16 activations / weight shadows (headline); f32: the reference's all-fp32 data flow on tf32 tensor cores")
     ap.add_argument("--bucket-mb", type=float, default=None,
                     help="fp32 MiB of gradients per fused all-reduce (0 = per layer; default: 80 from 2 ranks)")
     ap.add_argument("--no-e2e", action="store_true")
@@ -142,14 +144,15 @@ def run_ours(args, rank, local, world):
     from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer
     from fpga_ai_nic_b200.ops import kernels as K
     cfg = MLPConfig.reference(args.layers, args.width, args.mb)
-    cfg.fuse, cfg.codec, cfg.algo, cfg.bucket_mb = args.fuse, args.codec, args.algo, args.bucket_mb
+    cfg.fuse, cfg.codec, cfg.algo, cfg.bucket_mb, cfg.dtype = args.fuse, args.codec, args.algo, args.bucket_mb, args.dtype
+    f32 = args.dtype == "f32"
     tr = MLPTrainer(cfg)
     dev = tr.device
     g = torch.Generator().manual_seed(1234 + rank)
     nbuf = 4  # rotating synthetic batches, fp32 on the host like the reference's activations
     host_x = [(torch.rand(cfg.mb, cfg.sizes[0], generator=g) * 0.1 - 0.05).pin_memory() for _ in range(nbuf)]
     host_y = [torch.randint(0, cfg.sizes[-1], (cfg.mb,), generator=g, dtype=torch.int32).pin_memory() for _ in range(nbuf)]
-    dev_x = [K.cast_bf16(h.to(dev)) for h in host_x]
+    dev_x = [h.to(dev) if f32 else K.cast_bf16(h.to(dev)) for h in host_x]
     dev_y = [h.to(dev) for h in host_y]
 
     # ---- device-resident inputs: the kernel-level number
@@ -174,7 +177,7 @@ def run_ours(args, rank, local, world):
         def run_e2e(hx, steps, warmup):
             """hx: pinned host batches (fp32 like the reference's host activations, or bf16 as a loader that
             already emits the compute dtype would provide)."""
-            narrow = hx[0].dtype == torch.bfloat16
+            narrow = hx[0].dtype == torch.bfloat16 or f32      # staged batch is already in the compute dtype
             stage_in = [torch.empty(cfg.mb, cfg.sizes[0], dtype=hx[0].dtype, device=dev) for _ in range(2)]
             stage_bf16 = stage_in if narrow else [torch.empty(cfg.mb, cfg.sizes[0], dtype=torch.bfloat16, device=dev) for _ in range(2)]
             stage_y = [torch.empty(cfg.mb, dtype=torch.int32, device=dev) for _ in range(2)]
@@ -258,17 +261,19 @@ def run_ours(args, rank, local, world):
                        "host one step later (the last one before the closing event)"}
         loss = losses[-1]
         # same loop with the host batches already in the compute dtype (half the bytes over PCIe)
-        host_xb = [h.bfloat16().pin_memory() for h in host_x]
-        ms_b, losses_b = run_e2e(host_xb, args.steps, max(3, args.warmup))
-        e2e["bf16_host_inputs"] = {"value": cfg.mb * world * args.steps / (ms_b / 1e3), "ms_per_step": ms_b / args.steps,
-                                   "h2d_bytes_per_step": cfg.mb * cfg.sizes[0] * 2 + cfg.mb * 4, "loss": losses_b[-1]}
+        if not f32:
+            host_xb = [h.bfloat16().pin_memory() for h in host_x]
+            ms_b, losses_b = run_e2e(host_xb, args.steps, max(3, args.warmup))
+            e2e["bf16_host_inputs"] = {"value": cfg.mb * world * args.steps / (ms_b / 1e3), "ms_per_step": ms_b / args.steps,
+                                       "h2d_bytes_per_step": cfg.mb * cfg.sizes[0] * 2 + cfg.mb * 4, "loss": losses_b[-1]}
     ctr = tr.comm.counters()
     value = cfg.mb * world * args.steps / (ms / 1e3)
     gflops = cfg.flops_per_step(cfg.mb * world) / (ms / args.steps / 1e3) / 1e9
     out = {
         "metric": "mlp_train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "ours",
+        "scaling": "weak", "vs_baseline": None, "dtype": "tf32 (fp32 storage, kind::tf32 MMA)" if f32 else "bf16",
+        "data": "synthetic", "impl": "ours",
         "config": {"model": f"mlp_{cfg.nlayers}x{args.width}x{args.width}", "global_batch": cfg.mb * world,
                    "seq_len": 1, "parallelism": f"dp{world}", "per_rank_batch": cfg.mb, "fuse": cfg.fuse,
                    "optimizer": "sgd lr=0.1 fused into the gradient all-reduce", "master_weights": "fp32",

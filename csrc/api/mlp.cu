@@ -45,6 +45,7 @@ struct Layer {
 struct ainic_mlp {
   ainic_comm_t* comm = nullptr;
   int nlayers = 0, mb = 0, fuse = 0;
+  bool f32 = false;                  // all-fp32 data flow on kind::tf32 tensor cores (no bf16 anywhere)
   float lr = 0.1f, loss_weight = 0.1f;
   int codec = AINIC_CODEC_F32, bfp_mode = AINIC_BFP_CLEAN, algo = AINIC_ALGO_AUTO;
   int comm_ctas = 0, gemm_ctas = 0, wgrad_ctas = 0;
@@ -108,6 +109,13 @@ static int fail(const char* what) {
 
 extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlayers, const int* sizes, int mb, int fuse,
                                 float lr, float loss_weight, int codec, int bfp_mode, int algo) {
+  return ainic_mlp_create2(out, comm, nlayers, sizes, mb, fuse, lr, loss_weight, codec, bfp_mode, algo, 0);
+}
+
+extern "C" int ainic_mlp_create2(ainic_mlp_t** out, ainic_comm_t* comm, int nlayers, const int* sizes, int mb, int fuse,
+                                 float lr, float loss_weight, int codec, int bfp_mode, int algo, int compute_dtype) {
+  if (compute_dtype != 0 && compute_dtype != 1) return AINIC_ERR_ARG;
+  if (compute_dtype == 1 && fuse != 0) return AINIC_ERR_UNSUPPORTED;   // fp32 outputs have no bias / ReLU epilogue
   // mb is the K extent of the weight-gradient GEMM (TMA rows of 16 bytes: a multiple of 8 bf16 values)
   if (!out || !comm || nlayers < 1 || !sizes || mb < 8 || mb % 8) return AINIC_ERR_ARG;
   for (int i = 0; i <= nlayers; ++i)
@@ -122,20 +130,20 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
   m->codec = codec;
   m->bfp_mode = bfp_mode;
   m->algo = algo;
+  m->f32 = compute_dtype == 1;
   if (const char* e = getenv("AINIC_COMM_CTAS")) m->comm_ctas = atoi(e);
   if (const char* e = getenv("AINIC_GEMM_CTAS")) m->gemm_ctas = atoi(e);
   if (const char* e = getenv("AINIC_WGRAD_CTAS")) m->wgrad_ctas = atoi(e);
   // With a block-compressed wire format the weight-gradient GEMM can write the wire format itself (the
   // reference's BFP adapter sits right behind the adder tree the same way, hw/all_reduce.sv:745-772):
-  // no fp32 gradient in memory, no compression pass in the all-reduce.  The all-reduce gets shorter,
-  // the GEMM's exposed epilogue longer.  Measured on the reference MLP with 80 MiB buckets (ms/step,
-  // off -> on): 2 ranks 0.703 -> 0.710, 4 ranks 0.698 -> 0.657, 8 ranks 0.844 -> 0.800.  Default: on
-  // from 4 ranks; AINIC_FUSE_COMPRESS=0/1/2 overrides.
+  // no fp32 gradient in memory, no compression pass in the all-reduce.  Measured on the reference MLP
+  // (ms/step, off -> on, one fused call per 80 MiB bucket): 2 ranks 0.651 -> 0.586, 4 ranks 0.698 ->
+  // 0.657, 8 ranks 0.844 -> 0.800.  Default: on whenever there is a peer; AINIC_FUSE_COMPRESS=0/1/2 overrides.
   {
     const int n = ainic_comm_size(comm);
-    int mode = n >= 4 ? 1 : 0;
+    int mode = n >= 2 ? 1 : 0;
     if (const char* e = getenv("AINIC_FUSE_COMPRESS")) mode = atoi(e);
-    m->fuse_compress = mode >= 1 && n > 1 && (codec == AINIC_CODEC_BFP || codec == AINIC_CODEC_MXFP8);
+    m->fuse_compress = mode >= 1 && n > 1 && !m->f32 && (codec == AINIC_CODEC_BFP || codec == AINIC_CODEC_MXFP8);
     // AINIC_FUSE_COMPRESS=2: the epilogue also performs the reduce-scatter's data movement - each frame
     // is stored into the inbox of the rank that owns it, over NVLink, while the GEMM is still running.
     // Bit-identical results (scripts/mp_check.py 3b).  The frames are staged through shared memory and
@@ -155,8 +163,9 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
   TRY_CUDA(cudaEventCreateWithFlags(&m->fwd_done, cudaEventDisableTiming));
   TRY_CUDA(cudaMalloc(&m->loss_sum, 256));
   for (int l = 0; l <= nlayers; ++l) {
-    TRY_CUDA(cudaMalloc(&m->act[l], (size_t)mb * sizes[l] * 2));
-    if (l > 0) TRY_CUDA(cudaMalloc(&m->dact[l], (size_t)mb * sizes[l] * 2));
+    const size_t esz = m->f32 ? 4 : 2;
+    TRY_CUDA(cudaMalloc(&m->act[l], (size_t)mb * sizes[l] * esz));
+    if (l > 0) TRY_CUDA(cudaMalloc(&m->dact[l], (size_t)mb * sizes[l] * esz));
   }
   // Symmetric allocations, identical order on every rank: one arena per kind, a layer's slot is
   // its count rounded up to 1024 values (keeps every slot 4 KiB aligned and frame aligned; the pad
@@ -216,7 +225,9 @@ extern "C" int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlaye
     const int n = ainic_comm_size(comm);
     int want = n >= 2 ? 1 : 0;
     if (const char* e = getenv("AINIC_FLOW")) want = atoi(e);
-    m->flow = want != 0 && nlayers <= AINIC_FLOW_MAX_CHUNKS && !m->fuse_scatter;
+    // the flow kernel takes wire-format input: fp32, or frames written by the weight-gradient epilogue
+    const bool wire_ok = codec == AINIC_CODEC_F32 || m->fuse_compress;
+    m->flow = want != 0 && nlayers <= AINIC_FLOW_MAX_CHUNKS && !m->fuse_scatter && wire_ok && !m->f32;
   }
   if (m->flow) {
     TRY(ainic_comm_reserve_flow(comm, total, nlayers));
@@ -305,7 +316,8 @@ extern "C" void* ainic_mlp_buffer(ainic_mlp_t* m, int what, int l) {
 // Refresh every bf16 shadow from the fp32 masters (after init / checkpoint load).
 extern "C" int ainic_mlp_sync_shadows(ainic_mlp_t* m, void* stream) {
   if (!m) return AINIC_ERR_ARG;
-  for (auto& L : m->layers) TRY(ainic_cast_f32_bf16(L.w, L.wb, (size_t)L.in * L.out, stream));
+  if (!m->f32)
+    for (auto& L : m->layers) TRY(ainic_cast_f32_bf16(L.w, L.wb, (size_t)L.in * L.out, stream));
   m->first_step = true;
   return AINIC_OK;
 }
@@ -351,8 +363,12 @@ static int forward(ainic_mlp* m, cudaStream_t s, bool wait_updates) {
     epi.relu = relu ? 1 : 0;
     epi.mask_out = relu ? L.mask : nullptr;
     epi.alpha = 1.0f;
-    TRY(ainic_gemm_bf16(AINIC_GEMM_NT, m->act[l], L.in, L.wb, L.in, m->act[l + 1], L.out, m->mb, L.out, L.in, &epi, 0,
-                        m->gemm_ctas, s));
+    if (m->f32)   // fp32 activations x fp32 master weights on kind::tf32 (libxsmm_dnn_fc_fwd_exec_f32, :708-709)
+      TRY(ainic_gemm_tf32(AINIC_GEMM_NT, (const float*)m->act[l], L.in, L.w, L.in, (float*)m->act[l + 1], L.out, m->mb, L.out, L.in,
+                          nullptr, 0, m->gemm_ctas, s));
+    else
+      TRY(ainic_gemm_bf16(AINIC_GEMM_NT, m->act[l], L.in, L.wb, L.in, m->act[l + 1], L.out, m->mb, L.out, L.in, &epi, 0,
+                          m->gemm_ctas, s));
     m->launches++;
   }
   return AINIC_OK;
@@ -364,7 +380,7 @@ extern "C" int ainic_mlp_forward(ainic_mlp_t* m, const void* x_bf16, void* strea
   cudaStream_t s = (cudaStream_t)stream;
   if (m->events_stale) TRY_CUDA(cudaStreamWaitEvent(s, m->step_done, 0));
   if (x_bf16 != m->act[0])
-    TRY_CUDA(cudaMemcpyAsync(m->act[0], x_bf16, (size_t)m->mb * m->layers[0].in * 2, cudaMemcpyDeviceToDevice, s));
+    TRY_CUDA(cudaMemcpyAsync(m->act[0], x_bf16, (size_t)m->mb * m->layers[0].in * (m->f32 ? 4 : 2), cudaMemcpyDeviceToDevice, s));
   return forward(m, s, true);
 }
 
@@ -383,13 +399,17 @@ static int step_body(ainic_mlp* m, const void* x_bf16, const int32_t* labels, fl
   // in order, so layer 0's event covers all of them).
   if (!m->first_step) TRY_CUDA(cudaStreamWaitEvent(s, m->layers[0].dw_ready, 0));
   if (x_bf16 != m->act[0])
-    TRY_CUDA(cudaMemcpyAsync(m->act[0], x_bf16, (size_t)m->mb * m->layers[0].in * 2, cudaMemcpyDeviceToDevice, s));
+    TRY_CUDA(cudaMemcpyAsync(m->act[0], x_bf16, (size_t)m->mb * m->layers[0].in * (m->f32 ? 4 : 2), cudaMemcpyDeviceToDevice, s));
   if (m->profile) TRY_CUDA(cudaEventRecord(m->prof[0], s));
   TRY(forward(m, s, true));
   if (m->profile) TRY_CUDA(cudaEventRecord(m->prof[1], s));
   TRY_CUDA(cudaMemsetAsync(m->loss_sum, 0, 4, s));
-  TRY(ainic_softmax_xent(m->act[Ln], labels, nullptr, m->dact[Ln], m->loss_sum, m->mb, m->layers[Ln - 1].out,
-                         m->layers[Ln - 1].out, m->loss_weight, s));
+  if (m->f32)
+    TRY(ainic_softmax_xent_f32((const float*)m->act[Ln], labels, (float*)m->dact[Ln], m->loss_sum, m->mb, m->layers[Ln - 1].out,
+                               m->layers[Ln - 1].out, m->loss_weight, s));
+  else
+    TRY(ainic_softmax_xent(m->act[Ln], labels, nullptr, m->dact[Ln], m->loss_sum, m->mb, m->layers[Ln - 1].out,
+                           m->layers[Ln - 1].out, m->loss_weight, s));
   m->launches++;
   if (loss_out) TRY_CUDA(cudaMemcpyAsync(loss_out, m->loss_sum, 4, cudaMemcpyDeviceToDevice, s));
   if (relu) {  // the last layer's ReLU sits between the logits and the loss
@@ -464,8 +484,12 @@ static int step_body(ainic_mlp* m, const void* x_bf16, const int32_t* labels, fl
         we.scatter = &sc;
       }
     }
-    TRY(ainic_gemm_bf16(AINIC_GEMM_TN, m->dact[l + 1], L.out, m->act[l], L.in, cg ? nullptr : L.g, L.in, L.out, L.in,
-                        m->mb, &we, 0, m->wgrad_ctas, m->wgrad_stream));
+    if (m->f32)
+      TRY(ainic_gemm_tf32(AINIC_GEMM_TN, (const float*)m->dact[l + 1], L.out, (const float*)m->act[l], L.in, L.g, L.in, L.out, L.in,
+                          m->mb, nullptr, 0, m->wgrad_ctas, m->wgrad_stream));
+    else
+      TRY(ainic_gemm_bf16(AINIC_GEMM_TN, m->dact[l + 1], L.out, m->act[l], L.in, cg ? nullptr : L.g, L.in, L.out, L.in,
+                          m->mb, &we, 0, m->wgrad_ctas, m->wgrad_stream));
     m->launches++;
     if (use_bias) {
       TRY(ainic_bias_grad(m->dact[l + 1], L.dbias, m->mb, L.out, L.out, m->wgrad_stream));
@@ -481,8 +505,12 @@ static int step_body(ainic_mlp* m, const void* x_bf16, const int32_t* labels, fl
         de.done_flag = m->flow_ready + l;
         de.done_ticket = m->flow_tickets + 2 * l + 1;
       }
-      TRY(ainic_gemm_bf16(AINIC_GEMM_NN, m->dact[l + 1], L.out, L.wb, L.in, m->dact[l], L.in, m->mb, L.in, L.out, &de, 0,
-                          m->gemm_ctas, s));
+      if (m->f32)
+        TRY(ainic_gemm_tf32(AINIC_GEMM_NN, (const float*)m->dact[l + 1], L.out, L.w, L.in, (float*)m->dact[l], L.in, m->mb, L.in,
+                            L.out, nullptr, 0, m->gemm_ctas, s));
+      else
+        TRY(ainic_gemm_bf16(AINIC_GEMM_NN, m->dact[l + 1], L.out, L.wb, L.in, m->dact[l], L.in, m->mb, L.in, L.out, &de, 0,
+                            m->gemm_ctas, s));
       m->launches++;
       TRY_CUDA(cudaEventRecord(L.dx_done, s));
     }
@@ -497,7 +525,7 @@ static int step_body(ainic_mlp* m, const void* x_bf16, const int32_t* labels, fl
     ainic_allreduce_args_t a{};
     a.grad = L.g;
     a.weight = L.w;
-    a.weight_bf16 = L.wb;
+    a.weight_bf16 = m->f32 ? nullptr : L.wb;
     a.count = count;
     a.lr = m->lr;
     a.codec = m->codec;

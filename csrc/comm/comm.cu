@@ -50,7 +50,8 @@ struct ainic_comm {
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 // How many frames ahead of its loads a warp asks the L2 for local weights / gradients (AINIC_PF_DEPTH, 0 = off).
 static uint32_t pf_depth() {
-  static const uint32_t d = getenv("AINIC_PF_DEPTH") ? (uint32_t)atoi(getenv("AINIC_PF_DEPTH")) : 8u;
+  const char* e = getenv("AINIC_PF_DEPTH");   // read per call: cheap, and lets one process compare settings
+  const uint32_t d = e ? (uint32_t)atoi(e) : 8u;
   return d > 64 ? 64 : d;
 }
 // The ring inbox holds ceil(frames/(16N)) blocks x (2N-2) slices; rounding the block count up costs
@@ -424,6 +425,10 @@ extern "C" int ainic_allreduce_flow(ainic_comm_t* c, const ainic_allreduce_args_
   if (((uintptr_t)a->grad & 15) || ((uintptr_t)a->weight & 15) || ((uintptr_t)a->weight_bf16 & 7) || ((uintptr_t)a->grad_out & 15))
     return AINIC_ERR_ARG;
   if (a->grad_scattered) { set_error("flow: scattered input is not supported"); return AINIC_ERR_UNSUPPORTED; }
+  if (a->codec != AINIC_CODEC_F32 && !a->grad_compressed) {
+    set_error("flow: a compressed codec needs grad_compressed (frames written by the GEMM epilogue or a codec kernel)");
+    return AINIC_ERR_UNSUPPORTED;
+  }
   FlowFn kern = pick_flow(a->codec, a->bfp_mode);
   if (!kern) { set_error("unsupported codec"); return AINIC_ERR_UNSUPPORTED; }
   if (c->nranks > 1 && !ainic_comm_peer_ptr(c, a->grad, 0) && a->codec == AINIC_CODEC_F32) {
@@ -447,10 +452,11 @@ extern "C" int ainic_allreduce_flow(ainic_comm_t* c, const ainic_allreduce_args_
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (sms <= 0) sms = 148;
   }
-  int ctas = a->max_ctas > 0 ? a->max_ctas : sms;   // persistent: one CTA per SM, beside a GEMM CTA
-  if (ctas > kMaxCtas) ctas = kMaxCtas;
+  int ctas = a->max_ctas > 0 ? a->max_ctas : sms - 1;   // persistent workers beside the GEMM CTAs ...
+  if (ctas > sms - 1) ctas = sms - 1;
+  if (ctas < 1) ctas = 1;
   prefer_max_smem((const void*)kern);
-  kern<<<ctas, kCommThreadsOverlap, 0, (cudaStream_t)stream>>>(fc);
+  kern<<<ctas + 1, kCommThreadsOverlap, 0, (cudaStream_t)stream>>>(fc);   // ... plus the forwarder CTA
   CUDA_TRY(cudaGetLastError());
   return AINIC_OK;
 }
@@ -481,7 +487,7 @@ extern "C" int ainic_allreduce_flow_emulate(int nranks, float* grads, float* wei
   CUDA_TRY(cudaGetDevice(&dev));
   CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kCommThreadsOverlap, 0));
-  if ((long)ctas * nranks > (long)sms * per_sm) { set_error("emulation grid exceeds co-resident capacity"); return AINIC_ERR_ARG; }
+  if ((long)(ctas + 1) * nranks > (long)sms * per_sm) { set_error("emulation grid exceeds co-resident capacity"); return AINIC_ERR_ARG; }
   const size_t frames = bfp_frames(count);
   const size_t c_bytes = align_up(frames * 1024, 256), d_bytes = align_up((frames + (size_t)nchunks * nranks) * 2048, 256);
   const size_t flag_bytes = kFlagWords * sizeof(uint32_t), ctr_bytes = 256;
@@ -521,11 +527,18 @@ extern "C" int ainic_allreduce_flow_emulate(int nranks, float* grads, float* wei
     x.pf_depth = pf_depth();
     rc = fill_chunks(h[r], nranks, count, chunks, nchunks);
     h[r].local_ready = ready;
+    // the flow kernel takes its input in wire format: encode every rank's gradient into its stage C first
+    if (rc == AINIC_OK && codec != AINIC_CODEC_F32) {
+      x.precompressed = 1;
+      if (codec == AINIC_CODEC_BFP) rc = ainic_bfp_compress(x.grad, count, base(r), bfp_mode, s);
+      else if (codec == AINIC_CODEC_MXFP8) rc = ainic_mx_compress(x.grad, count, base(r), s);
+      else rc = ainic_cast_f32_bf16(x.grad, base(r), count, s);
+    }
   }
   if (rc == AINIC_OK && e == cudaSuccess) e = cudaMemcpyAsync(d_ctx, h, sizeof(FlowCtx) * nranks, cudaMemcpyHostToDevice, s);
   const FlowCtx* arg0 = d_ctx;
   void* args[] = {(void*)&arg0};
-  if (rc == AINIC_OK && e == cudaSuccess) e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas, nranks), dim3(kCommThreadsOverlap), args, 0, s);
+  if (rc == AINIC_OK && e == cudaSuccess) e = cudaLaunchCooperativeKernel((const void*)kern, dim3(ctas + 1, nranks), dim3(kCommThreadsOverlap), args, 0, s);
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   unsigned long long ctr[8] = {};
   if (rc == AINIC_OK && e == cudaSuccess) cudaMemcpy(ctr, h[0].c.counters, sizeof(ctr), cudaMemcpyDeviceToHost);

@@ -1,27 +1,32 @@
 // Flow all-reduce: ONE persistent launch walks a whole bucket chunk by chunk (in the trainer a chunk is
-// a layer), each chunk going through the two-shot steps of allreduce.cuh as soon as its producer
-// says it is complete:
+// a layer).  Every WARP is an independent pipeline with one role; nothing in the data path ever waits
+// on a CTA-wide barrier:
 //
-//   chunk k   local ready (the weight-gradient GEMM's last CTA raised the chunk's flag)
-//             -> [compress]  -> tell every peer "my chunk k is readable"          (flag phase 4)
-//             -> while that message travels: pull + apply the published shards of chunk k - 1
-//             -> all peers ready: reduce my 1/N of chunk k in fp32, SGD, publish it re-encoded
-//             -> tell every peer "my shard of chunk k is published"               (flag phase 5)
+//   forwarder   one warp (an extra CTA): watches the local doorbell of chunk k - the counter the
+//               weight-gradient GEMM's last CTA bumps when every tile is stored - and pushes
+//               "rank r's chunk k is readable" to every rank                          (flag phase 4)
+//   reduce      waits until chunk k is readable on every rank, pulls its frames of this rank's 1/N of
+//               the chunk from all ranks, sums in fp32 in rank order, applies SGD, publishes the sum
+//               re-encoded; the LAST reduce warp of the rank to finish chunk k (local ticket) tells
+//               every peer "rank r's shard of chunk k is published"                   (flag phase 5)
+//   gather      waits for a peer's published shard of chunk k, pulls its frames, applies SGD
 //
 // This is the reference's two-deep request pipeline (sw/mlp_mpi_example_f32.cpp:735-788: layer i's
-// all-reduce runs under layer i-1's backward GEMMs) taken to its limit.  The host issues nothing
-// per layer; the readiness signal is a device flag written by the GEMM epilogue ("epilogue flips the
-// ready flag"), the cross-GPU flag round trips of chunk k hide behind the data movement of chunk
-// k - 1, and what is left exposed after the last weight-gradient GEMM is one chunk's reduce + gather
-// instead of a whole multi-layer bucket's.  The NIC of the reference starts on a buffer when the
-// host rings the doorbell (hw/all_reduce.sv:210-244); here the doorbell is rung by the producer kernel.
+// all-reduce runs under layer i-1's backward GEMMs) taken to its limit: the host issues nothing per
+// layer, the doorbell is rung by the producer kernel ("epilogue flips the ready flag"; the NIC of the
+// reference starts when the host writes the start CSR, hw/all_reduce.sv:210-244), reduce of chunk
+// k + 1 and gather of chunk k run at the same time in different warps, and what is left exposed after
+// the last weight-gradient GEMM is one chunk's reduce + gather.
+// (A first version kept all warps of a CTA in lock step - compress, signal, gather, wait, reduce,
+// signal, with CTA barriers in between: every phase of every chunk paid its own pipeline ramp and
+// two system-scope fences; measured 0.88 vs 0.65 ms/step at 2 GPUs against one fused call per bucket.)
 //
-// Flags: CTA b of a rank only waits for CTA b of its peers, as in allreduce.cuh.  Values are
-// (call number << 8) | (k + 1), monotonically increasing over chunks and calls; the call number
-// lives in device memory, so launch arguments are identical from call to call (graph replay).
-// No staging parity is needed: a rank leaves call s only after every peer has published every shard,
-// i.e. after every peer has finished reading this rank's stage C, and a peer's READY(0) of call s + 1
-// can only be sent after it has finished reading this rank's stage D in call s.
+// The input must already be in wire format: frames written by the GEMM epilogue (precompressed) or
+// plain fp32 (codec 0).  Flag values are the call number, kept in device memory (identical launch
+// arguments from call to call: graph replay); one flag word per (source rank, chunk), single writer.
+// No staging parity is needed: a rank leaves call s only after it has pulled every peer's published
+// shards, i.e. after every peer has finished reading this rank's frames, and a peer's "readable" of
+// call s + 1 can only be sent after that peer has left call s.
 #pragma once
 #include "allreduce.cuh"
 
@@ -46,23 +51,53 @@ struct FlowCtx {
                                    // caller before the producers of this call are launched
 };
 
-// Thread 0 polls the producer's flag; everyone leaves together.
-__device__ __forceinline__ void wait_local_ready(const FlowCtx& fc, int k, WaitStats& ws) {
-  const int idx = fc.chunk[k].ready_idx;
-  if (fc.local_ready && idx >= 0 && threadIdx.x == 0) {
+// ---- flag words (inside the per-rank flag area of the communicator; see flag_index)
+//   [phase 4][src][k]       rank src's chunk k is readable          (written by src's forwarder)
+//   [phase 5][src][k]       rank src's shard of chunk k is published (written by src's last reduce warp)
+//   [phase 5][src][48]      rank src has pulled everything it needs  (fp32 in-place variant only)
+//   [phase 5][self][64 + k] local ticket of the reduce warps for chunk k; [64 + 48] of the gather warps
+constexpr int kFlowDoneSlot = 48, kFlowTicketBase = 64;
+static_assert(kMaxChunks <= kFlowDoneSlot && kFlowTicketBase + kFlowDoneSlot < kMaxCtas, "flow flag slots");
+
+// Lanes 0 .. N-1 of a warp poll one flag each (lane p: source rank p; skip_self leaves out this rank).
+__device__ __forceinline__ void warp_wait_flags(const RankCtx& c, int phase, int slot, uint32_t value, bool skip_self, int lane,
+                                                WaitStats& ws) {
+  if (lane < c.nranks && !(skip_self && lane == c.rank)) {
+    const uint32_t* f = c.flags[c.rank] + flag_index(phase, lane, slot);
     unsigned long long t0 = 0;
     uint32_t polls = 0;
-    const uint32_t need = fc.chunk[k].ready_need ? fc.chunk[k].ready_need : 1u;
-    while (ptx::ld_acquire_gpu(fc.local_ready + idx) < need) {
-      __nanosleep(polls > 16 ? 512 : 128);   // a GEMM CTA shares this SM: stay out of its issue slots
+    while ((int)(ptx::ld_acquire_sys(f) - value) < 0) {
+      __nanosleep(polls > 32 ? 1024 : (polls > 4 ? 256 : 64));   // GEMM CTAs share this SM: stay out of their issue slots
       if ((++polls & 0xFFu) == 0) {
         const unsigned long long now = ptx::globaltimer_ns();
         if (t0 == 0) t0 = now;
-        else if (now - t0 > fc.c.timeout_ns) { atomicAdd(&ws.timeouts, 1u); break; }
+        else if (now - t0 > c.timeout_ns) { atomicAdd(&ws.timeouts, 1u); break; }
       }
     }
   }
-  __syncthreads();
+  __syncwarp();
+}
+// Lanes 0 .. N-1 store `value` into slot [phase][this rank][slot] of every rank (lane p -> rank p).
+__device__ __forceinline__ void warp_post_flags(const RankCtx& c, int phase, int slot, uint32_t value, bool skip_self, int lane) {
+  if (lane < c.nranks && !(skip_self && lane == c.rank)) {
+    __threadfence_system();
+    ptx::st_release_sys(c.flags[lane] + flag_index(phase, c.rank, slot), value);
+  }
+}
+// A warp has finished its part of something `total` warps of this rank work on; returns true in the
+// last one (all lanes).  The ticket word resets itself.
+__device__ __forceinline__ bool warp_ticket_last(const RankCtx& c, int slot, uint32_t total, int lane) {
+  __syncwarp();
+  uint32_t last = 0;
+  if (lane == 0) {
+    __threadfence();   // this warp's stores before its ticket (the last warp then fences at system scope)
+    uint32_t* t = c.flags[c.rank] + flag_index(kPhaseFlowPub, c.rank, kFlowTicketBase + slot);
+    if (atomicAdd(t, 1u) == total - 1u) {
+      *reinterpret_cast<volatile uint32_t*>(t) = 0u;
+      last = 1;
+    }
+  }
+  return __shfl_sync(kFullMask, last, 0) != 0;
 }
 
 __device__ __forceinline__ uint32_t flow_shard(const FlowChunk& ch, int N) { return (ch.frames + (uint32_t)N - 1u) / (uint32_t)N; }
@@ -70,117 +105,119 @@ __device__ __forceinline__ uint32_t flow_shard_lim(const FlowChunk& ch, int N, i
   const uint32_t sh = flow_shard(ch, N), lo = (uint32_t)s * sh;
   return ch.frames <= lo ? 0u : (ch.frames - lo < sh ? ch.frames - lo : sh);
 }
-// The three data phases sit inside one loop over the chunks.  Passing the values their address
-// arithmetic derives from through an empty asm keeps the compiler from hoisting that arithmetic out of
-// the chunk loop and holding it in registers across the other phases.  (ptxas still parks a few
-// just-loaded frame words in local memory between request and use - ~300 bytes per thread, L1-resident,
-// a handful of instructions per 512-value frame.)
-__device__ __forceinline__ void launder(uint32_t& first, uint32_t& step, int& lane) {
-  asm volatile("" : "+r"(first), "+r"(step), "+r"(lane));
-}
-template <int CODEC, int MODE>
-__device__ __forceinline__ void flow_compress(const RankCtx& c, const FlowChunk ch, uint32_t first, uint32_t step, int lane) {
-  launder(first, step, lane);
-  const int N = c.nranks;
-  const uint32_t shard = flow_shard(ch, N);
-  for (int s = 0; s < N; ++s) {
-    const uint32_t base = ch.frame0 + (uint32_t)s * shard, lim = flow_shard_lim(ch, N, s);
-#pragma unroll 1
-    for (uint32_t j0 = first; j0 < lim; j0 += 2 * step) {
-      if (c.pf_depth) {
-        const uint32_t ja = j0 + c.pf_depth * 2 * step;
-        if (ja < lim) prefetch_frame_f32(c.grad, base + ja, lane);
-        if (ja + step < lim) prefetch_frame_f32(c.grad, base + ja + step, lane);
-      }
-      compress_pair<CODEC, MODE>(c, 0, base + j0, base + j0 + step, j0 + step < lim, lane);
-    }
-  }
-}
-template <int CODEC, int MODE>
-__device__ __forceinline__ void flow_reduce(const RankCtx& c, const FlowChunk ch, uint32_t first, uint32_t step, int lane) {
-  launder(first, step, lane);
-  using FC = FrameCodec<CODEC, MODE>;
-  const int N = c.nranks;
-  const uint32_t shard = flow_shard(ch, N);
-  const uint32_t base = ch.frame0 + (uint32_t)c.rank * shard, lim = flow_shard_lim(ch, N, c.rank);
-  const uint32_t d_off = ch.d_off;
-  auto src = [&](int p, uint32_t j) -> const uint8_t* {
-    return CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + (size_t)(base + j) * 2048
-                      : c.stage_c[p] + (size_t)(base + j) * FC::kBytes;
-  };
-  reduce_stream<CODEC, MODE>(c, base, first, step, lim, lane, src, [&](uint32_t j, float (&acc)[16], float (&w)[16]) {
-    if constexpr (CODEC == 0) {
-      // in place: peers pull the reduced shard out of my gradient buffer
-      if (N > 1) frame_store_f32(c.grad + (size_t)(base + j) * kFrameVals, kFrameVals, acc, lane);
-    } else {
-      // publish into my stage D, then apply exactly what the peers will decode
-      frame_encode_rt<CODEC, MODE>(acc, c.stage_d[c.rank] + (size_t)(d_off + j) * FC::kBytes, lane);
-    }
-    apply_full_w(c, base + j, acc, w, lane);
-  });
-}
-template <int CODEC, int MODE>
-__device__ __forceinline__ void flow_gather(const RankCtx& c, const FlowChunk ch, uint32_t first, uint32_t step, int lane) {
-  launder(first, step, lane);
-  gather_stream<CODEC, MODE>(c, flow_shard(ch, c.nranks), ch.frames, first, step, lane, ch.frame0, ch.d_off);
-}
 
-template <int CODEC, int MODE>
-__device__ void flow_body(const FlowCtx& fc, int cta, int nctas, WaitStats& ws) {
+// The forwarder: local doorbells -> "readable" flags on every rank (this one included).
+__device__ void flow_forward(const FlowCtx& fc, WaitStats& ws, int lane) {
   const RankCtx& c = fc.c;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-  const int N = c.nranks, K = fc.nchunks;
-  const uint32_t first = (uint32_t)cta + (uint32_t)warp * nctas, step = (uint32_t)nctas * wpb;
-  const uint32_t vbase = ws.epoch << 8;
-  // One loop body for "start chunk k" and "finish chunk k - 1" (k = K only finishes).
-#pragma unroll 1
-  for (int k = 0; k <= K; ++k) {
-    if (k < K) {
-      // 1. chunk k is complete on this rank; compress it unless the producer already wrote frames
-      wait_local_ready(fc, k, ws);
-      if (k == 0) mark_phase(ws, 0);
-      if (CODEC != 0 && !c.precompressed) flow_compress<CODEC, MODE>(c, fc.chunk[k], first, step, lane);
-      if (N > 1) signal_all(c, kPhaseFlowReady, cta, vbase | (uint32_t)(k + 1));
+  for (int k = 0; k < fc.nchunks; ++k) {
+    const int idx = fc.chunk[k].ready_idx;
+    if (fc.local_ready && idx >= 0 && lane == 0) {
+      const uint32_t need = fc.chunk[k].ready_need ? fc.chunk[k].ready_need : 1u;
+      unsigned long long t0 = 0;
+      uint32_t polls = 0;
+      while (ptx::ld_acquire_gpu(fc.local_ready + idx) < need) {
+        __nanosleep(128);
+        if ((++polls & 0x3FFu) == 0) {
+          const unsigned long long now = ptx::globaltimer_ns();
+          if (t0 == 0) t0 = now;
+          else if (now - t0 > c.timeout_ns) { atomicAdd(&ws.timeouts, 1u); break; }
+        }
+      }
     }
-    // 2. while that flag travels: pull + apply the previous chunk's published shards
-    if (N > 1 && k > 0) {
-      wait_all(c, kPhaseFlowPub, cta, vbase | (uint32_t)k, ws);
-      if (k == K) mark_phase(ws, 1);
-      flow_gather<CODEC, MODE>(c, fc.chunk[k - 1], first, step, lane);
-    }
-    if (k == K) break;
-    // 3. my shard of chunk k: fp32 sum in rank order, publish re-encoded, apply what peers will decode
-    if (N > 1) wait_all(c, kPhaseFlowReady, cta, vbase | (uint32_t)(k + 1), ws);
-    flow_reduce<CODEC, MODE>(c, fc.chunk[k], first, step, lane);
-    if (N > 1) signal_all(c, kPhaseFlowPub, cta, vbase | (uint32_t)(k + 1));
-  }
-  if (CODEC == 0 && N > 1) {   // peers read my gradient in place: do not return (and let the next GEMM overwrite it) before they are done
-    signal_all(c, kPhaseFlowReady, cta, vbase | 0xFEu);
-    wait_all(c, kPhaseFlowReady, cta, vbase | 0xFEu, ws);
+    __syncwarp();
+    if (k == 0 && lane == 0) ws.mark[0] = ptx::globaltimer_ns();
+    warp_post_flags(c, kPhaseFlowReady, k, ws.epoch, false, lane);
   }
 }
 
 template <int CODEC, int MODE>
-__device__ __forceinline__ void run_flow(const FlowCtx& fc, int cta, int nctas) {
+__device__ void flow_reduce_role(const FlowCtx& fc, WaitStats& ws, uint32_t first, uint32_t step, uint32_t nwarps, int lane) {
+  using FC = FrameCodec<CODEC, MODE>;
+  const RankCtx& c = fc.c;
+  const int N = c.nranks;
+#pragma unroll 1
+  for (int k = 0; k < fc.nchunks; ++k) {
+    const FlowChunk ch = fc.chunk[k];
+    warp_wait_flags(c, kPhaseFlowReady, k, ws.epoch, false, lane, ws);
+    const uint32_t shard = flow_shard(ch, N);
+    const uint32_t base = ch.frame0 + (uint32_t)c.rank * shard, lim = flow_shard_lim(ch, N, c.rank);
+    const uint32_t d_off = ch.d_off;
+    auto src = [&](int p, uint32_t j) -> const uint8_t* {
+      return CODEC == 0 ? reinterpret_cast<const uint8_t*>(c.peer_grad[p]) + (size_t)(base + j) * 2048
+                        : c.stage_c[p] + (size_t)(base + j) * FC::kBytes;
+    };
+    reduce_stream<CODEC, MODE>(c, base, first, step, lim, lane, src, [&](uint32_t j, float (&acc)[16], float (&w)[16]) {
+      if constexpr (CODEC == 0) {
+        // in place: peers pull the reduced shard out of my gradient buffer
+        if (N > 1) frame_store_f32(c.grad + (size_t)(base + j) * kFrameVals, kFrameVals, acc, lane);
+      } else {
+        // publish into my stage D, then apply exactly what the peers will decode
+        frame_encode_rt<CODEC, MODE>(acc, c.stage_d[c.rank] + (size_t)(d_off + j) * FC::kBytes, lane);
+      }
+      apply_full_w(c, base + j, acc, w, lane);
+    });
+    if (N > 1 && warp_ticket_last(c, k, nwarps, lane)) warp_post_flags(c, kPhaseFlowPub, k, ws.epoch, true, lane);
+  }
+}
+
+template <int CODEC, int MODE>
+__device__ void flow_gather_role(const FlowCtx& fc, WaitStats& ws, uint32_t first, uint32_t step, uint32_t nwarps, bool timekeeper,
+                                 int lane) {
+  const RankCtx& c = fc.c;
+#pragma unroll 1
+  for (int k = 0; k < fc.nchunks; ++k) {
+    const FlowChunk ch = fc.chunk[k];
+    warp_wait_flags(c, kPhaseFlowPub, k, ws.epoch, true, lane, ws);
+    if (timekeeper && k == fc.nchunks - 1 && lane == 0) ws.mark[1] = ptx::globaltimer_ns();
+    gather_stream<CODEC, MODE>(c, flow_shard(ch, c.nranks), ch.frames, first, step, lane, ch.frame0, ch.d_off);
+  }
+  if (CODEC == 0) {
+    // peers read my gradient in place: nobody may leave (and let the next GEMM overwrite its gradient)
+    // before every rank has pulled what it needs
+    if (warp_ticket_last(c, kFlowDoneSlot, nwarps, lane)) warp_post_flags(c, kPhaseFlowPub, kFlowDoneSlot, ws.epoch, true, lane);
+    warp_wait_flags(c, kPhaseFlowPub, kFlowDoneSlot, ws.epoch, true, lane, ws);
+  }
+}
+
+// How many of a CTA's 8 warps reduce (the rest gather): a rank reduces 1/N of the frames and gathers the rest.
+__device__ __forceinline__ int flow_reduce_warps(int nranks, int wpb) {
+  if (nranks <= 1) return wpb;
+  const int r = (wpb + nranks / 2) / nranks;
+  return r < 1 ? 1 : (r > wpb - 1 ? wpb - 1 : r);
+}
+
+// Grid: gridDim.x - 1 worker CTAs + one forwarder CTA (the last).
+template <int CODEC, int MODE>
+__device__ __forceinline__ void run_flow(const FlowCtx& fc, int cta, int nctas_total) {
   __shared__ WaitStats ws;
   if (threadIdx.x == 0) begin_call(fc.c, ws);
   const unsigned long long t0 = ptx::globaltimer_ns();
   __syncthreads();
-  flow_body<CODEC, MODE>(fc, cta, nctas, ws);
+  const RankCtx& c = fc.c;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int workers = nctas_total - 1;
+  if (cta == workers) {
+    if (warp == 0) flow_forward(fc, ws, lane);
+  } else {
+    const int nr = flow_reduce_warps(c.nranks, wpb), ng = wpb - nr;
+    if (warp < nr) flow_reduce_role<CODEC, MODE>(fc, ws, (uint32_t)(cta * nr + warp), (uint32_t)(workers * nr), (uint32_t)(workers * nr), lane);
+    else flow_gather_role<CODEC, MODE>(fc, ws, (uint32_t)(cta * ng + warp - nr), (uint32_t)(workers * ng), (uint32_t)(workers * ng),
+                                       cta == 0 && warp == nr, lane);
+  }
   __syncthreads();
   if (threadIdx.x == 0) {
     const unsigned long long t1 = ptx::globaltimer_ns();
-    const RankCtx& c = fc.c;
     if (ws.timeouts) atomicAdd(c.counters + CTR_TIMEOUTS, (unsigned long long)ws.timeouts);
+    if (cta == workers) {   // forwarder: when the first chunk became readable here
+      if (ws.mark[0]) atomicAdd(c.counters + CTR_TO_BARRIER0_NS, ws.mark[0] - t0);
+    }
     if (cta == 0) {
       atomicAdd(c.counters + CTR_BUSY_NS, t1 - t0);
-      atomicAdd(c.counters + CTR_WAIT_NS, ws.wait_ns);
       atomicAdd(c.counters + CTR_LAUNCHES, 1ull);
       c.counters[CTR_LAST_NS] = t1 - t0;
-      if (ws.mark[0]) atomicAdd(c.counters + CTR_TO_BARRIER0_NS, ws.mark[0] - t0);   // kernel start -> first chunk ready locally
       if (ws.mark[1]) atomicAdd(c.counters + CTR_TO_BARRIER1_NS, t1 - ws.mark[1]);   // last chunk published everywhere -> end (the exposed tail)
     }
-    end_call(c, ws, nctas);
+    end_call(c, ws, nctas_total);
   }
 }
 

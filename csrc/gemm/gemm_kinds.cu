@@ -265,3 +265,236 @@ gemm_kind_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     tmem_dealloc<kTmemCols>(tmem_base);
   }
 }
+
+// ------------------------------------------------------------------------------------------ MX quantisers
+// byte offset of the scale of (row r, K-block kblock) inside the atom-tiled scale array of an operand with K values per row
+__host__ __device__ inline size_t sf_offset(int r, int kblock, int K) {
+  const size_t atom = (size_t)(r >> 7) * (size_t)(K >> 7) + (size_t)(kblock >> 2);
+  return atom * 512 + (size_t)(r & 31) * 16 + (size_t)((r & 127) >> 5) * 4 + (size_t)(kblock & 3);
+}
+__device__ __forceinline__ float load_as_f32(const void* p, size_t i, bool bf16) {
+  return bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i]) : reinterpret_cast<const float*>(p)[i];
+}
+// Blocks of 32 consecutive values along the contiguous dimension (K-major operands): one thread per block.
+__global__ void mx_quantize_rows_kernel(const void* x, bool bf16, int rows, int K, int ld, uint8_t* q, uint8_t* sf) {
+  const int kblocks = K >> 5;
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (size_t)rows * kblocks) return;
+  const int r = (int)(t / kblocks), kb = (int)(t % kblocks);
+  float v[32];
+  uint32_t E = 0;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    v[j] = load_as_f32(x, (size_t)r * ld + kb * 32 + j, bf16);
+    E = max(E, bfp_exp_field(__float_as_uint(v[j])));
+  }
+  const uint32_t sb = mx_scale_byte(E);
+  const float inv = mx_inv_scale(sb);
+  uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+  for (int j = 0; j < 32; ++j) w[j >> 2] |= f32_to_e4m3(v[j] * inv) << (8 * (j & 3));
+  uint4* dst = reinterpret_cast<uint4*>(q + (size_t)r * K + kb * 32);
+  dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+  dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  sf[sf_offset(r, kb, K)] = (uint8_t)sb;
+}
+// Blocks of 32 consecutive ROWS of one column (MN-major operands: x is [K][cols], K is the slow dimension):
+// one thread per (column, row block); adjacent threads take adjacent columns, so every row access is coalesced.
+__global__ void mx_quantize_cols_kernel(const void* x, bool bf16, int K, int cols, int ld, uint8_t* q, uint8_t* sf) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int kblocks = K >> 5;
+  if (t >= (size_t)cols * kblocks) return;
+  const int c = (int)(t % cols), kb = (int)(t / cols);
+  float v[32];
+  uint32_t E = 0;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    v[j] = load_as_f32(x, (size_t)(kb * 32 + j) * ld + c, bf16);
+    E = max(E, bfp_exp_field(__float_as_uint(v[j])));
+  }
+  const uint32_t sb = mx_scale_byte(E);
+  const float inv = mx_inv_scale(sb);
+#pragma unroll
+  for (int j = 0; j < 32; ++j) q[(size_t)(kb * 32 + j) * cols + c] = (uint8_t)f32_to_e4m3(v[j] * inv);
+  sf[sf_offset(c, kb, K)] = (uint8_t)sb;
+}
+
+// ------------------------------------------------------------------------------------------ host
+template <int KIND>
+static int kind_tmap(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_c, uint32_t box_r) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return AINIC_ERR_CUDA;
+  constexpr int elem = Kind<KIND>::kElem;
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstride[1] = {ld * elem};
+  cuuint32_t box[2] = {box_c, box_r};
+  cuuint32_t estr[2] = {1, 1};
+  const CUtensorMapDataType dt = KIND == KIND_TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
+  CUresult r = fn(map, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? AINIC_OK : AINIC_ERR_CUDA;
+}
+
+template <int KIND, int BLOCK_N, bool A_MN, bool B_MN, int OUT>
+static int launch_kind(const void* a, int lda, const void* b, int ldb, const EpiParams& ep, const MxParams& mx, int max_ctas,
+                       cudaStream_t stream) {
+  using T = Kind<KIND>;
+  constexpr int kSpan = kStageKBytes / T::kElem;
+  CUtensorMap ta, tb;
+  int rc;
+  // K-major: global [rows][K], box = kBlockK x rows.  MN-major: global [K][rows], box = one 128-byte span x kBlockK.
+  if (A_MN) rc = kind_tmap<KIND>(&ta, a, ep.K, ep.M, lda, kSpan, T::kBlockK);
+  else rc = kind_tmap<KIND>(&ta, a, ep.M, ep.K, lda, T::kBlockK, BLOCK_M);
+  if (rc) return rc;
+  if (B_MN) rc = kind_tmap<KIND>(&tb, b, ep.K, ep.N, ldb, kSpan, T::kBlockK);
+  else rc = kind_tmap<KIND>(&tb, b, ep.N, ep.K, ldb, T::kBlockK, BLOCK_N);
+  if (rc) return rc;
+  auto kern = gemm_kind_kernel<KIND, BLOCK_N, A_MN, B_MN, OUT>;
+  constexpr int smem = kinds_num_stages(BLOCK_N, KIND) * kinds_stage_bytes(BLOCK_N, KIND) + 1024 + 256;
+  static_assert(smem <= 227 * 1024, "shared memory budget");
+  static bool configured = false;
+  if (!configured) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return AINIC_ERR_CUDA;
+    configured = true;
+  }
+  const int tiles = ((ep.M + BLOCK_M - 1) / BLOCK_M) * ((ep.N + BLOCK_N - 1) / BLOCK_N);
+  int grid = num_sms();
+  if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+  if (tiles < grid) grid = tiles;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(192);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  if (cudaLaunchKernelEx(&cfg, kern, ta, tb, ep, mx) != cudaSuccess) return AINIC_ERR_CUDA;
+  return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
+}
+
+static int pick_block_n(int M, int N, const int* cand, int ncand, int sms) {
+  double best = -1.0;
+  int bn = cand[0];
+  for (int i = 0; i < ncand; ++i) {
+    const long tiles = (long)((M + 127) / 128) * ((N + cand[i] - 1) / cand[i]);
+    const long waves = (tiles + sms - 1) / sms;
+    const double e = ((double)M * N) / ((double)waves * sms * 128 * (cand[i] + 24.0));
+    if (e > best * 1.02) { best = e; bn = cand[i]; }
+  }
+  return bn;
+}
+
+}  // namespace gemm
+}  // namespace ainic
+
+using namespace ainic::gemm;
+
+static int fill_epi(EpiParams& ep, void* c, int ldc, int M, int N, int K, const ainic_gemm_epilogue_t* epi) {
+  ep.c = c;
+  ep.M = M; ep.N = N; ep.K = K; ep.ldc = ldc;
+  ep.alpha = 1.0f;
+  ep.epi_sleep = gemm_epi_sleep_ns();
+  if (epi) {
+    if (epi->cgrad || epi->scatter) return AINIC_ERR_UNSUPPORTED;   // compressed epilogues: bf16 kernel only
+    ep.bias = epi->bias;
+    ep.mask_out = epi->mask_out;
+    ep.mask_in = epi->mask_in;
+    ep.relu = epi->relu;
+    ep.accumulate = epi->accumulate;
+    ep.alpha = epi->alpha;
+    ep.done_flag = epi->done_flag;
+    ep.done_ticket = epi->done_ticket;
+    if (ep.done_flag) return AINIC_ERR_UNSUPPORTED;                 // doorbells: bf16 kernel only
+  }
+  return AINIC_OK;
+}
+
+#define KIND_CASE(KIND, BN, AMN, BMN, OUT) \
+  case BN: return launch_kind<KIND, BN, AMN, BMN, OUT>(a, lda, b, ldb, ep, mx, max_ctas, (cudaStream_t)stream);
+
+// fp32 operands on the tensor cores as tf32, fp32 result (alpha / accumulate epilogue).  Layouts as ainic_gemm_bf16.
+extern "C" int ainic_gemm_tf32(int layout, const float* a, int lda, const float* b, int ldb, float* c, int ldc, int M, int N,
+                               int K, const ainic_gemm_epilogue_t* epi, int block_n, int max_ctas, void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || !a || !b || !c) return AINIC_ERR_ARG;
+  if ((N % 8) || (K % 4) || (lda % 4) || (ldb % 4) || (ldc % 4)) return AINIC_ERR_ARG;
+  if (((uintptr_t)a & 15) || ((uintptr_t)b & 15) || ((uintptr_t)c & 15)) return AINIC_ERR_ARG;
+  EpiParams ep{};
+  int rc = fill_epi(ep, c, ldc, M, N, K, epi);
+  if (rc) return rc;
+  if (ep.bias || ep.relu || ep.mask_in || ep.mask_out) return AINIC_ERR_UNSUPPORTED;   // fp32 outputs: scale / accumulate only
+  MxParams mx{};
+  const int sms = (max_ctas > 0 && max_ctas < num_sms()) ? max_ctas : num_sms();
+  if (block_n == 0) {
+    const int cand[] = {256, 192, 128};
+    block_n = pick_block_n(M, N, cand, 3, sms);
+  }
+  switch (layout) {
+    case AINIC_GEMM_NT:
+      switch (block_n) { KIND_CASE(KIND_TF32, 256, false, false, OUT_FP32) KIND_CASE(KIND_TF32, 192, false, false, OUT_FP32)
+                         KIND_CASE(KIND_TF32, 128, false, false, OUT_FP32) default: return AINIC_ERR_ARG; }
+    case AINIC_GEMM_NN:
+      switch (block_n) { KIND_CASE(KIND_TF32, 256, false, true, OUT_FP32) KIND_CASE(KIND_TF32, 192, false, true, OUT_FP32)
+                         KIND_CASE(KIND_TF32, 128, false, true, OUT_FP32) default: return AINIC_ERR_ARG; }
+    case AINIC_GEMM_TN:
+      switch (block_n) { KIND_CASE(KIND_TF32, 256, true, true, OUT_FP32) KIND_CASE(KIND_TF32, 192, true, true, OUT_FP32)
+                         KIND_CASE(KIND_TF32, 128, true, true, OUT_FP32) default: return AINIC_ERR_ARG; }
+  }
+  return AINIC_ERR_ARG;
+}
+
+extern "C" size_t ainic_mx_sf_bytes(size_t rows, size_t K) { return ((rows + 127) / 128) * (K / 128) * 512; }
+
+// x: [rows][ld] (K contiguous) fp32 or bf16 -> q: [rows][K] e4m3 + scale atoms (one ue8m0 per 32 values along K)
+extern "C" int ainic_mx_quantize_rows(const void* x, int x_is_bf16, int rows, int K, int ld, void* q, void* sf, void* stream) {
+  if (!x || !q || !sf || rows <= 0 || K <= 0 || (K % 128) || ld < K || ((uintptr_t)q & 15)) return AINIC_ERR_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (cudaMemsetAsync(sf, 0, ainic_mx_sf_bytes(rows, K), s) != cudaSuccess) return AINIC_ERR_CUDA;
+  const size_t n = (size_t)rows * (K / 32);
+  mx_quantize_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, x_is_bf16 != 0, rows, K, ld, static_cast<uint8_t*>(q),
+                                                                       static_cast<uint8_t*>(sf));
+  return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
+}
+// x: [K][ld] (cols contiguous) -> q: [K][cols] e4m3 + scale atoms indexed (column, K-block): blocks of 32 consecutive rows
+extern "C" int ainic_mx_quantize_cols(const void* x, int x_is_bf16, int K, int cols, int ld, void* q, void* sf, void* stream) {
+  if (!x || !q || !sf || cols <= 0 || K <= 0 || (K % 128) || ld < cols) return AINIC_ERR_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (cudaMemsetAsync(sf, 0, ainic_mx_sf_bytes(cols, K), s) != cudaSuccess) return AINIC_ERR_CUDA;
+  const size_t n = (size_t)cols * (K / 32);
+  mx_quantize_cols_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, x_is_bf16 != 0, K, cols, ld, static_cast<uint8_t*>(q),
+                                                                       static_cast<uint8_t*>(sf));
+  return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
+}
+
+// e4m3 operands with ue8m0 block scales (32 values along K), scales applied by the tensor core.
+// NT: a [M][lda], b [N][ldb] (K contiguous).  NN: a [M][lda], b [K][ldb].  TN: a [K][lda] (M contiguous), b [K][ldb].
+// sfa / sfb: scale atoms from ainic_mx_quantize_rows (K-contiguous operands) / _cols (K-slow operands).
+extern "C" int ainic_gemm_mxfp8(int layout, const void* a, int lda, const void* sfa, const void* b, int ldb, const void* sfb,
+                                void* c, int ldc, int out_fp32, int M, int N, int K, const ainic_gemm_epilogue_t* epi,
+                                int block_n, int max_ctas, void* stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || !a || !b || !c || !sfa || !sfb) return AINIC_ERR_ARG;
+  if ((N % 8) || (K % 128) || (lda % 16) || (ldb % 16) || (ldc % 8)) return AINIC_ERR_ARG;
+  if (((uintptr_t)a & 15) || ((uintptr_t)b & 15) || ((uintptr_t)c & 15) || ((uintptr_t)sfa & 15) || ((uintptr_t)sfb & 15)) return AINIC_ERR_ARG;
+  EpiParams ep{};
+  int rc = fill_epi(ep, c, ldc, M, N, K, epi);
+  if (rc) return rc;
+  if (out_fp32 && (ep.bias || ep.relu || ep.mask_in || ep.mask_out)) return AINIC_ERR_UNSUPPORTED;
+  MxParams mx{static_cast<const uint8_t*>(sfa), static_cast<const uint8_t*>(sfb)};
+  if (block_n == 0) block_n = 128;   // two accumulator stages; 256 trades the epilogue overlap for half the B traffic
+  if (out_fp32) {
+    switch (layout) {
+      case AINIC_GEMM_NT: switch (block_n) { KIND_CASE(KIND_MXF8, 128, false, false, OUT_FP32) KIND_CASE(KIND_MXF8, 256, false, false, OUT_FP32) default: return AINIC_ERR_ARG; }
+      case AINIC_GEMM_NN: switch (block_n) { KIND_CASE(KIND_MXF8, 128, false, true, OUT_FP32) KIND_CASE(KIND_MXF8, 256, false, true, OUT_FP32) default: return AINIC_ERR_ARG; }
+      case AINIC_GEMM_TN: switch (block_n) { KIND_CASE(KIND_MXF8, 128, true, true, OUT_FP32) KIND_CASE(KIND_MXF8, 256, true, true, OUT_FP32) default: return AINIC_ERR_ARG; }
+    }
+  } else {
+    switch (layout) {
+      case AINIC_GEMM_NT: switch (block_n) { KIND_CASE(KIND_MXF8, 128, false, false, OUT_BF16) KIND_CASE(KIND_MXF8, 256, false, false, OUT_BF16) default: return AINIC_ERR_ARG; }
+      case AINIC_GEMM_NN: switch (block_n) { KIND_CASE(KIND_MXF8, 128, false, true, OUT_BF16) KIND_CASE(KIND_MXF8, 256, false, true, OUT_BF16) default: return AINIC_ERR_ARG; }
+      case AINIC_GEMM_TN: switch (block_n) { KIND_CASE(KIND_MXF8, 128, true, true, OUT_BF16) KIND_CASE(KIND_MXF8, 256, true, true, OUT_BF16) default: return AINIC_ERR_ARG; }
+    }
+  }
+  return AINIC_ERR_ARG;
+}

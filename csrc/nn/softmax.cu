@@ -85,6 +85,42 @@ __global__ void __launch_bounds__(128) softmax_xent_kernel(const __nv_bfloat16* 
   }
 }
 
+// Same kernel for the all-fp32 ("f32" / tf32) configuration: fp32 logits in, fp32 dlogits out.
+__global__ void __launch_bounds__(128) softmax_xent_f32_kernel(const float* __restrict__ logits, const int32_t* __restrict__ labels,
+                                                               float* __restrict__ dlogits, float* __restrict__ loss_sum, int mb,
+                                                               int n, int ld, float loss_weight) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= mb) return;
+  const float4* src = reinterpret_cast<const float4*>(logits + (size_t)row * ld);
+  const int n4 = n >> 2;
+  float m = -CUDART_INF_F;
+  for (int i = lane; i < n4; i += 32) {
+    const float4 f = src[i];
+    m = fmaxf(fmaxf(m, fmaxf(f.x, f.y)), fmaxf(f.z, f.w));
+  }
+  m = warp_max(m);
+  float s = 0.0f;
+  for (int i = lane; i < n4; i += 32) {
+    const float4 f = src[i];
+    s += __expf(f.x - m) + __expf(f.y - m) + __expf(f.z - m) + __expf(f.w - m);
+  }
+  s = warp_sum(s);
+  const float inv = 1.0f / s;
+  const int lab = labels[row];
+  const float scale = loss_weight / (float)mb;
+  for (int i = lane; i < n4; i += 32) {
+    const float4 f = src[i];
+    float4 d;
+    d.x = scale * (__expf(f.x - m) * inv - ((i * 4 + 0) == lab ? 1.0f : 0.0f));
+    d.y = scale * (__expf(f.y - m) * inv - ((i * 4 + 1) == lab ? 1.0f : 0.0f));
+    d.z = scale * (__expf(f.z - m) * inv - ((i * 4 + 2) == lab ? 1.0f : 0.0f));
+    d.w = scale * (__expf(f.w - m) * inv - ((i * 4 + 3) == lab ? 1.0f : 0.0f));
+    reinterpret_cast<float4*>(dlogits + (size_t)row * ld)[i] = d;
+  }
+  if (lane == 0 && loss_sum) atomicAdd(loss_sum, -(logits[(size_t)row * ld + lab] - m - __logf(s)));
+}
+
 // dbias[c] = sum_r dy[r][c]; block = 32 column-pairs x 8 row groups, atomics across row chunks.
 __global__ void __launch_bounds__(256) bias_grad_kernel(const __nv_bfloat16* __restrict__ dy, float* __restrict__ dbias,
                                                         int mb, int n, int ld, int rows_per_block) {
@@ -152,6 +188,14 @@ extern "C" int ainic_softmax_xent(const void* logits, const int32_t* labels, voi
   softmax_xent_kernel<<<(mb + rows_per_block - 1) / rows_per_block, 128, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)logits, labels, (__nv_bfloat16*)probs, (__nv_bfloat16*)dlogits, loss_sum, mb, n, ld,
       loss_weight);
+  return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
+}
+
+extern "C" int ainic_softmax_xent_f32(const float* logits, const int32_t* labels, float* dlogits, float* loss_sum, int mb, int n,
+                                      int ld, float loss_weight, void* stream) {
+  if (!logits || !labels || !dlogits || mb <= 0 || n <= 0 || (n % 4) || (ld % 4) || ((uintptr_t)logits & 15) || ((uintptr_t)dlogits & 15))
+    return AINIC_ERR_ARG;
+  softmax_xent_f32_kernel<<<(mb + 3) / 4, 128, 0, (cudaStream_t)stream>>>(logits, labels, dlogits, loss_sum, mb, n, ld, loss_weight);
   return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
 }
 

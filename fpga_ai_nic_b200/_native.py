@@ -150,6 +150,14 @@ def cuda() -> C.CDLL:
     lib.ainic_cast_f32_bf16.argtypes = [vp, vp, sz, vp]
     lib.ainic_gemm_bf16.argtypes = [C.c_int, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.POINTER(GemmEpilogue), C.c_int, C.c_int, vp]
+    lib.ainic_gemm_tf32.argtypes = [C.c_int, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int,
+                                    C.POINTER(GemmEpilogue), C.c_int, C.c_int, vp]
+    lib.ainic_mx_sf_bytes.restype = sz
+    lib.ainic_mx_sf_bytes.argtypes = [sz, sz]
+    lib.ainic_mx_quantize_rows.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp]
+    lib.ainic_mx_quantize_cols.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp]
+    lib.ainic_gemm_mxfp8.argtypes = [C.c_int, vp, C.c_int, vp, vp, C.c_int, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                     C.POINTER(GemmEpilogue), C.c_int, C.c_int, vp]
     lib.ainic_softmax_xent.argtypes = [vp, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, vp]
     lib.ainic_bias_grad.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp]
     lib.ainic_comm_create.argtypes = [C.POINTER(vp), C.c_int, C.c_int, sz]
@@ -180,6 +188,9 @@ def cuda() -> C.CDLL:
                                                     C.c_int, vp, C.c_char_p, sz]
     lib.ainic_mlp_create.argtypes = [C.POINTER(vp), vp, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_float,
                                      C.c_float, C.c_int, C.c_int, C.c_int]
+    lib.ainic_mlp_create2.argtypes = [C.POINTER(vp), vp, C.c_int, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_float,
+                                      C.c_float, C.c_int, C.c_int, C.c_int, C.c_int]
+    lib.ainic_softmax_xent_f32.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, vp]
     lib.ainic_mlp_destroy.argtypes = [vp]
     lib.ainic_mlp_buffer.restype = vp
     lib.ainic_mlp_buffer.argtypes = [vp, C.c_int, C.c_int]

@@ -31,6 +31,8 @@ class MLPConfig:
     algo: str = "auto"
     seed: int = 1                                              # libxsmm_rng_set_seed(1), :273
     init_scale: float = 1.0                                    # multiplies the reference init (wide layers need < 1)
+    dtype: str = "bf16"                                        # "bf16": bf16 activations / weight shadows (kind::f16 MMA);
+                                                               # "f32": the reference's all-fp32 data flow on kind::tf32 MMA
     bucket_mb: float | None = None                             # fp32 MiB of gradients per all-reduce call; 0 = per
                                                                # layer (reference, :754); None = 80 from 2 ranks, else 0
 
@@ -118,8 +120,9 @@ class MLPTrainer:
         if cfg.bucket_mb is not None:
             os.environ["AINIC_BUCKET_MB"] = repr(float(cfg.bucket_mb))
         try:
-            N.check(self.lib.ainic_mlp_create(C.byref(h), self.comm.handle, cfg.nlayers, sizes, cfg.mb, cfg.fuse, cfg.lr,
-                                              cfg.loss_weight, self.codec, cfg.bfp_mode, self.algo), "mlp_create")
+            N.check(self.lib.ainic_mlp_create2(C.byref(h), self.comm.handle, cfg.nlayers, sizes, cfg.mb, cfg.fuse, cfg.lr,
+                                               cfg.loss_weight, self.codec, cfg.bfp_mode, self.algo,
+                                               {"bf16": 0, "f32": 1}[cfg.dtype]), "mlp_create")
         finally:
             if cfg.bucket_mb is not None:
                 if saved is None:
@@ -128,6 +131,7 @@ class MLPTrainer:
                     os.environ["AINIC_BUCKET_MB"] = saved
         self.handle = h
         self.device = self.comm.device
+        self.act_dtype = torch.float32 if cfg.dtype == "f32" else torch.bfloat16
         self.loss_dev = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._views: dict = {}
         self.init_weights()
@@ -141,6 +145,8 @@ class MLPTrainer:
         key = (what, layer)
         if key not in self._views:
             code, dt = self._WHAT[what]
+            if what in ("act", "dact"):
+                dt = self.act_dtype
             ptr = self.lib.ainic_mlp_buffer(self.handle, code, layer)
             if not ptr:
                 raise KeyError(key)
@@ -201,7 +207,7 @@ class MLPTrainer:
 
     # -- execution ------------------------------------------------------------------------------
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        assert x.dtype == torch.bfloat16 and x.is_cuda and x.is_contiguous()
+        assert x.dtype == self.act_dtype and x.is_cuda and x.is_contiguous()
         N.check(self.lib.ainic_mlp_forward(self.handle, x.data_ptr(), N.stream_ptr()), "mlp_forward")
         return self.buffer("act", self.cfg.nlayers)
 
@@ -210,7 +216,7 @@ class MLPTrainer:
         """One training iteration (enqueue only).  Returns the device scalar holding this rank's
         summed cross-entropy (divide by mb for the mean); ``loss_out`` (fp32[1], device) replaces the
         trainer's own scalar, e.g. to keep several steps' losses in flight."""
-        assert x.dtype == torch.bfloat16 and x.is_cuda and x.is_contiguous()
+        assert x.dtype == self.act_dtype and x.is_cuda and x.is_contiguous()
         assert labels.dtype == torch.int32 and labels.is_cuda
         dst = loss_out if loss_out is not None else self.loss_dev
         N.check(self.lib.ainic_mlp_step(self.handle, x.data_ptr(), labels.data_ptr(),

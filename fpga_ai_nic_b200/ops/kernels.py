@@ -264,3 +264,77 @@ def allreduce_flow_emulate(grads: torch.Tensor, weights: torch.Tensor | None, lr
     N.check(rc, "allreduce_flow_emulate")
     _count()
     return gout, weights, shadow
+
+
+# ---------------------------------------------------------------- tf32 and MX block-scaled GEMMs (csrc/gemm/gemm_kinds.cu)
+def gemm_tf32(layout: int, a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None, alpha: float = 1.0,
+              accumulate: bool = False, block_n: int = 0, max_ctas: int = 0) -> torch.Tensor:
+    """fp32 operands on the tensor cores as tf32, fp32 result.  Layouts as the bf16 GEMM:
+    GEMM_NT  c[M,N] = a[M,K] @ b[N,K]^T;  GEMM_NN  c[M,N] = a[M,K] @ b[K,N];  GEMM_TN  c[M,N] = a[K,M]^T @ b[K,N]."""
+    _chk(a, torch.float32)
+    _chk(b, torch.float32)
+    if layout == GEMM_NT:
+        (M, K), Nn = a.shape, b.shape[0]
+    elif layout == GEMM_NN:
+        (M, K), Nn = a.shape, b.shape[1]
+    else:
+        (K, M), Nn = a.shape, b.shape[1]
+    if out is None:
+        out = torch.empty(M, Nn, dtype=torch.float32, device=a.device)
+    epi = N.GemmEpilogue(None, None, None, alpha, 0, int(accumulate))
+    rc = N.cuda().ainic_gemm_tf32(layout, a.data_ptr(), a.stride(0), b.data_ptr(), b.stride(0), out.data_ptr(), out.stride(0),
+                                  M, Nn, K, C.byref(epi), block_n, max_ctas, N.stream_ptr())
+    N.check(rc, "gemm_tf32")
+    _count()
+    return out
+
+
+def mx_sf_bytes(rows: int, k: int) -> int:
+    return N.cuda().ainic_mx_sf_bytes(rows, k)
+
+
+def mx_quantize_rows(x: torch.Tensor):
+    """x [rows, K] (fp32 / bf16, K contiguous) -> (q uint8 [rows, K] e4m3, scale atoms uint8): one ue8m0 scale per 32
+    consecutive values of a row, stored in the tcgen05 scale-factor atom layout (gemm_kinds.cu)."""
+    assert x.is_cuda and x.dim() == 2 and x.stride(1) == 1 and x.dtype in (torch.float32, torch.bfloat16)
+    rows, k = x.shape
+    q = torch.empty(rows, k, dtype=torch.uint8, device=x.device)
+    sf = torch.empty(mx_sf_bytes(rows, k), dtype=torch.uint8, device=x.device)
+    N.check(N.cuda().ainic_mx_quantize_rows(x.data_ptr(), int(x.dtype == torch.bfloat16), rows, k, x.stride(0), q.data_ptr(),
+                                            sf.data_ptr(), N.stream_ptr()), "mx_quantize_rows")
+    _count(2)
+    return q, sf
+
+
+def mx_quantize_cols(x: torch.Tensor):
+    """x [K, cols] (K is the slow dimension) -> (q uint8 [K, cols], scale atoms): one scale per 32 consecutive ROWS of a
+    column - the operand form of the backward-weight product, where K is the minibatch."""
+    assert x.is_cuda and x.dim() == 2 and x.stride(1) == 1 and x.dtype in (torch.float32, torch.bfloat16)
+    k, cols = x.shape
+    q = torch.empty(k, cols, dtype=torch.uint8, device=x.device)
+    sf = torch.empty(mx_sf_bytes(cols, k), dtype=torch.uint8, device=x.device)
+    N.check(N.cuda().ainic_mx_quantize_cols(x.data_ptr(), int(x.dtype == torch.bfloat16), k, cols, x.stride(0), q.data_ptr(),
+                                            sf.data_ptr(), N.stream_ptr()), "mx_quantize_cols")
+    _count(2)
+    return q, sf
+
+
+def gemm_mxfp8(layout: int, a: torch.Tensor, sfa: torch.Tensor, b: torch.Tensor, sfb: torch.Tensor, out_dtype=torch.bfloat16,
+               out: torch.Tensor | None = None, block_n: int = 0, max_ctas: int = 0) -> torch.Tensor:
+    """e4m3 operands + ue8m0 block scales, scaled inside the tensor core (tcgen05.mma.kind::mxf8f6f4.block_scale)."""
+    _chk(a, torch.uint8)
+    _chk(b, torch.uint8)
+    if layout == GEMM_NT:
+        (M, K), Nn = a.shape, b.shape[0]
+    elif layout == GEMM_NN:
+        (M, K), Nn = a.shape, b.shape[1]
+    else:
+        (K, M), Nn = a.shape, b.shape[1]
+    if out is None:
+        out = torch.empty(M, Nn, dtype=out_dtype, device=a.device)
+    rc = N.cuda().ainic_gemm_mxfp8(layout, a.data_ptr(), a.stride(0), sfa.data_ptr(), b.data_ptr(), b.stride(0), sfb.data_ptr(),
+                                   out.data_ptr(), out.stride(0), int(out.dtype == torch.float32), M, Nn, K, None, block_n,
+                                   max_ctas, N.stream_ptr())
+    N.check(rc, "gemm_mxfp8")
+    _count()
+    return out

@@ -57,6 +57,7 @@ CUDA_SOURCES = [
     "nn/softmax.cu",
     "gemm/gemm_tcgen05.cu",
     "gemm/gemm_tcgen05_2cta.cu",
+    "gemm/gemm_kinds.cu",
     "comm/comm.cu",
     "comm/nvls.cu",
     "comm/emulate_noalloc.cu",

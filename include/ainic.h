@@ -98,10 +98,36 @@ typedef struct ainic_gemm_epilogue {
 int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b, int ldb, void* c, int ldc, int M, int N,
                     int K, const ainic_gemm_epilogue_t* epi, int block_n, int max_ctas, void* stream);
 
+/* fp32 operands on the tensor cores as tf32 (tcgen05.mma.kind::tf32), fp32 result with the alpha / accumulate
+ * epilogue; layouts as ainic_gemm_bf16.  The tensor-core form of the reference's all-fp32 MLP
+ * (libxsmm_dnn_fc_*_exec_f32, sw/mlp_mpi_example_f32.cpp:708-709, :741-742): no bf16 rounding anywhere.
+ * N % 8 == 0, K / lda / ldb / ldc % 4 == 0. */
+int ainic_gemm_tf32(int layout, const float* a, int lda, const float* b, int ldb, float* c, int ldc, int M, int N, int K,
+                    const ainic_gemm_epilogue_t* epi, int block_n, int max_ctas, void* stream);
+
+/* MX block-scaled fp8 GEMM (K14): e4m3 operands with one ue8m0 scale per 32 values along K, multiplied by
+ * tcgen05.mma.kind::mxf8f6f4.block_scale - the tensor core reads the scales from tensor memory.  The block
+ * geometry is the MXFP8 wire codec's (and the 32-value generalisation of the reference's 16-value
+ * shared-exponent blocks, hw/bfp_adapter.sv:59-76).  Scales travel in 512-byte "atoms" covering 128 rows x
+ * 4 K-blocks: byte (r % 32) * 16 + (r / 32) * 4 + kb, atoms laid out [rows / 128][K / 128].
+ *   ainic_mx_quantize_rows   x [rows][ld], K contiguous  -> q [rows][K] e4m3 + atoms   (operands of NT; A of NN)
+ *   ainic_mx_quantize_cols   x [K][ld], K the slow dim   -> q [K][cols] e4m3 + atoms   (operands of TN; B of NN)
+ * Same bytes and scales as ainic_mx_compress on the same 32-value blocks.  K % 128 == 0. */
+size_t ainic_mx_sf_bytes(size_t rows, size_t K);
+int ainic_mx_quantize_rows(const void* x, int x_is_bf16, int rows, int K, int ld, void* q, void* sf, void* stream);
+int ainic_mx_quantize_cols(const void* x, int x_is_bf16, int K, int cols, int ld, void* q, void* sf, void* stream);
+/* c = bf16 (bias / ReLU / mask epilogue) or fp32 (alpha / accumulate); block_n 128 (default) or 256. */
+int ainic_gemm_mxfp8(int layout, const void* a_e4m3, int lda, const void* sfa, const void* b_e4m3, int ldb, const void* sfb,
+                     void* c, int ldc, int out_fp32, int M, int N, int K, const ainic_gemm_epilogue_t* epi, int block_n,
+                     int max_ctas, void* stream);
+
 /* Row softmax + cross-entropy; dlogits = loss_weight*(p - onehot)/mb as bf16; loss_sum += sum_i CE_i.
  * (libxsmm_dnn_smax_{fwd,bwd}_exec_f32, sw/mlp_mpi_example_f32.cpp:718-728) */
 int ainic_softmax_xent(const void* logits_bf16, const int32_t* labels, void* probs_bf16 /*nullable*/,
                        void* dlogits_bf16, float* loss_sum, int mb, int n, int ld, float loss_weight, void* stream);
+/* fp32 logits / dlogits variant for the all-fp32 (tf32 tensor core) configuration */
+int ainic_softmax_xent_f32(const float* logits, const int32_t* labels, float* dlogits, float* loss_sum, int mb, int n, int ld,
+                           float loss_weight, void* stream);
 /* x[i] = mask[i] ? x[i] : 0 on bf16 data (ReLU backward of the loss gradient); count % 8 == 0 */
 int ainic_apply_mask_bf16(void* x_bf16, const uint8_t* mask, size_t count, void* stream);
 /* dbias[n] = sum over rows of dy[mb][n] (bf16 in, fp32 out) */
@@ -226,6 +252,11 @@ int ainic_allreduce_emulate_noalloc(int nranks, float* grads, float* weights, vo
 typedef struct ainic_mlp ainic_mlp_t;
 int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlayers, const int* sizes, int mb, int fuse, float lr,
                      float loss_weight, int codec, int bfp_mode, int algo);
+/* compute_dtype: 0 = bf16 activations / weight shadows on kind::f16 tensor cores (ainic_mlp_create); 1 = the
+ * reference's all-fp32 data flow on kind::tf32 tensor cores: fp32 activations, GEMMs read the fp32 master
+ * weights directly, no shadow (fuse must be 0; x passed to step/forward is fp32). */
+int ainic_mlp_create2(ainic_mlp_t** out, ainic_comm_t* comm, int nlayers, const int* sizes, int mb, int fuse, float lr,
+                      float loss_weight, int codec, int bfp_mode, int algo, int compute_dtype);
 int ainic_mlp_destroy(ainic_mlp_t* m);
 /* what: 0 weight f32, 1 grad f32, 2 shadow bf16, 3 bias f32, 4 dbias f32, 5 act bf16, 6 dact bf16, 7 relu mask */
 void* ainic_mlp_buffer(ainic_mlp_t* m, int what, int layer);

@@ -223,3 +223,43 @@ def test_flow_mode_same_bits_as_per_layer_calls(monkeypatch, graph, fuse):
         assert torch.equal(a, b)
     for a, b in zip(out["0"][1], out["1"][1]):
         assert torch.equal(a, b)
+
+
+def test_f32_mode_matches_fp32_oracle():
+    """dtype="f32": fp32 activations and master weights straight into kind::tf32 tensor cores - the reference's
+    all-fp32 MLP (libxsmm_dnn_fc_*_exec_f32).  Compared with the fp32 CPU oracle WITHOUT any bf16 rounding,
+    at tf32 tolerance; the shadow-free update must leave the masters as the only copy."""
+    from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer
+    cfg = MLPConfig(sizes=[256, 384, 256, 128], mb=256, fuse=0, lr=0.5, loss_weight=1.0, dtype="f32")
+    tr = MLPTrainer(cfg)
+    g = torch.Generator().manual_seed(12)
+    x = torch.rand(cfg.mb, cfg.sizes[0], generator=g) * 2 - 1
+    y = torch.randint(0, cfg.sizes[-1], (cfg.mb,), generator=g, dtype=torch.int32)
+    w0 = [tr.buffer("weight", l).cpu().clone() for l in range(cfg.nlayers)]
+    xd, yd = x.cuda(), y.cuda()
+    losses = []
+    for _ in range(3):
+        tr.step(xd, yd)
+        tr.wait()
+        torch.cuda.synchronize()
+        losses.append(float(tr.loss_dev.item()) / cfg.mb)
+    W = [w.clone() for w in w0]
+    ref = []
+    for _ in range(3):
+        acts = [x]
+        for l in range(cfg.nlayers):
+            acts.append(acts[-1] @ W[l].t())
+        loss, _, d = O.softmax_loss(acts[-1], y, cfg.loss_weight)
+        ref.append(loss)
+        for l in reversed(range(cfg.nlayers)):
+            dw = d.t() @ acts[l]
+            dn = d @ W[l]
+            W[l] = O.sgd(W[l], dw, cfg.lr)
+            d = dn
+    for a, r in zip(losses, ref):
+        assert abs(a - r) <= 5e-3 * abs(r) + 1e-3, (losses, ref)
+    for l in range(cfg.nlayers):
+        upd = (W[l] - w0[l]).norm().clamp_min(1e-12)
+        assert ((tr.buffer("weight", l).cpu() - W[l]).norm() / upd).item() < 5e-3
+    assert tr.buffer("act", 1).dtype == torch.float32
+    tr.close()
