@@ -95,6 +95,44 @@ def _run(cmd: list[str], log: Path | None = None) -> None:
         raise RuntimeError(f"build step failed: {cmd[0]} ... {cmd[-1]}")
 
 
+def _content_hash(srcs: list[Path]) -> str:
+    """Hash of everything a library is built from (its sources, every header, the flags).  Staleness is
+    decided by content, not by mtime: a copied tree (the GPU boxes get a snapshot) has arbitrary mtimes."""
+    import hashlib
+    h = hashlib.sha1()
+    hs = sorted(list(CSRC.rglob("*.h")) + list(CSRC.rglob("*.cuh")) + list((ROOT / "include").glob("*.h")))
+    for f in sorted(srcs) + hs:
+        h.update(str(f.relative_to(ROOT)).encode())
+        h.update(f.read_bytes())
+    h.update(" ".join(NVCC_FLAGS[:-6] + CXX_FLAGS[:-4]).encode())
+    return h.hexdigest()
+
+
+def _lib_current(out: Path, srcs: list[Path]) -> bool:
+    side = out.with_suffix(out.suffix + ".srchash")
+    try:
+        return out.exists() and out.stat().st_size > 0 and side.read_text().strip() == _content_hash(srcs)
+    except OSError:
+        return False
+
+
+class _BuildLock:
+    """One builder at a time per tree (N ranks importing the package at once must not all compile and
+    overwrite the same .so): an advisory lock on a file in the library directory."""
+
+    def __enter__(self):
+        import fcntl
+        LIBDIR.mkdir(parents=True, exist_ok=True)
+        self.fh = open(LIBDIR / ".build.lock", "w")
+        fcntl.flock(self.fh, fcntl.LOCK_EX)
+        return self
+
+    def __exit__(self, *a):
+        import fcntl
+        fcntl.flock(self.fh, fcntl.LOCK_UN)
+        self.fh.close()
+
+
 def _existing(rel: list[str], base: Path) -> list[Path]:
     return [base / r for r in rel if (base / r).exists()]
 
@@ -103,8 +141,14 @@ def build_oracle(force: bool = False) -> Path:
     LIBDIR.mkdir(parents=True, exist_ok=True)
     out = LIBDIR / "libainic_oracle.so"
     srcs = _existing(ORACLE_SOURCES, CSRC)
-    if force or _stale(out, srcs, _deps_mtime()):
-        _run([CXX, *CXX_FLAGS, "-shared", "-o", str(out), *map(str, srcs), "-lpthread"])
+    if not force and _lib_current(out, srcs):
+        return out
+    with _BuildLock():
+        if force or not _lib_current(out, srcs):      # somebody else may have built it while we waited
+            tmp = out.with_suffix(f".tmp{os.getpid()}.so")
+            _run([CXX, *CXX_FLAGS, "-shared", "-o", str(tmp), *map(str, srcs), "-lpthread"])
+            os.replace(tmp, out)
+            out.with_suffix(out.suffix + ".srchash").write_text(_content_hash(srcs))
     return out
 
 
@@ -113,6 +157,15 @@ def build_cuda(force: bool = False, jobs: int | None = None) -> Path:
     OBJDIR.mkdir(parents=True, exist_ok=True)
     out = LIBDIR / "libainic_cuda.so"
     srcs = _existing(CUDA_SOURCES, CSRC)
+    if not force and _lib_current(out, srcs):
+        return out
+    with _BuildLock():
+        if not force and _lib_current(out, srcs):
+            return out
+        return _build_cuda_locked(out, srcs, force, jobs)
+
+
+def _build_cuda_locked(out: Path, srcs: list[Path], force: bool, jobs: int | None) -> Path:
     hdr = _deps_mtime()
     objs, todo = [], []
     for s in srcs:
@@ -129,9 +182,11 @@ def build_cuda(force: bool = False, jobs: int | None = None) -> Path:
     if todo:
         with cf.ThreadPoolExecutor(max_workers=jobs or min(8, os.cpu_count() or 4)) as ex:
             list(ex.map(compile_one, todo))
-    if todo or not out.exists():
-        _run([NVCC, "-shared", "-o", str(out), *map(str, objs), "-gencode", "arch=compute_100a,code=sm_100a",
-              "--cudart=static", "-ccbin", CXX, "-lpthread", "-ldl", "-lrt"])
+    tmp = out.with_suffix(f".tmp{os.getpid()}.so")
+    _run([NVCC, "-shared", "-o", str(tmp), *map(str, objs), "-gencode", "arch=compute_100a,code=sm_100a",
+          "--cudart=static", "-ccbin", CXX, "-lpthread", "-ldl", "-lrt"])
+    os.replace(tmp, out)          # atomic: a concurrent dlopen sees the old or the new library, never half of one
+    out.with_suffix(out.suffix + ".srchash").write_text(_content_hash(srcs))
     return out
 
 
