@@ -220,10 +220,14 @@ extern "C" int ainic_mlp_create2(ainic_mlp_t** out, ainic_comm_t* comm, int nlay
     }
   }
   {
-    // Flow mode: default from 2 ranks (AINIC_FLOW=0/1 overrides; 1 also works on a single rank, where the
-    // persistent kernel degenerates to a per-layer SGD pass that starts as soon as the layer's dW exists).
+    // Flow mode (AINIC_FLOW=1): opt-in.  Correct at every world size (bit-identical to one call per bucket), but
+    // measured slower: 2 ranks 1.03-1.08 ms/step against 0.56-0.59 with one fused call per 80 MiB bucket.  The
+    // per-layer time line (AINIC_FLOW_TRACE) shows why: a reduce warp needs ~58 us for its ~7 frames of a layer
+    // and ~15 us more for the ticket / flag fences, against one layer of GEMMs every ~33 us, so the kernel falls
+    // behind from the second layer on (profiles/README.md, section "flow mode").
     const int n = ainic_comm_size(comm);
-    int want = n >= 2 ? 1 : 0;
+    (void)n;
+    int want = 0;
     if (const char* e = getenv("AINIC_FLOW")) want = atoi(e);
     // the flow kernel takes wire-format input: fp32, or frames written by the weight-gradient epilogue
     const bool wire_ok = codec == AINIC_CODEC_F32 || m->fuse_compress;

@@ -49,7 +49,14 @@ struct FlowCtx {
   int nchunks;
   const uint32_t* local_ready;     // device words counting finished producers of each chunk (nullable); zeroed by the
                                    // caller before the producers of this call are launched
+  unsigned long long* trace;       // nullable: [5][kMaxChunks] %globaltimer stamps of the last call (ns since kernel start of
+                                   // CTA 0 / the forwarder): doorbell seen, reduce got READY, reduce done, gather got PUB, gather done
+  unsigned long long t_origin;     // unused on the host side
 };
+constexpr int kTraceDoorbell = 0, kTraceReduceGo = 1, kTraceReduceDone = 2, kTraceGatherGo = 3, kTraceGatherDone = 4;
+__device__ __forceinline__ void flow_stamp(const FlowCtx& fc, int what, int k, bool on, int lane) {
+  if (fc.trace && on && lane == 0) fc.trace[what * kMaxChunks + k] = ptx::globaltimer_ns();
+}
 
 // ---- flag words (inside the per-rank flag area of the communicator; see flag_index)
 //   [phase 4][src][k]       rank src's chunk k is readable          (written by src's forwarder)
@@ -66,14 +73,18 @@ __device__ __forceinline__ void warp_wait_flags(const RankCtx& c, int phase, int
     const uint32_t* f = c.flags[c.rank] + flag_index(phase, lane, slot);
     unsigned long long t0 = 0;
     uint32_t polls = 0;
-    while ((int)(ptx::ld_acquire_sys(f) - value) < 0) {
-      __nanosleep(polls > 32 ? 1024 : (polls > 4 ? 256 : 64));   // GEMM CTAs share this SM: stay out of their issue slots
+    // Poll with RELAXED loads and fence once at the end: an acquire load at system scope carries a fence
+    // that invalidates the SM's L1 every time, and a thousand warps polling that way (measured: 0.95 ms per
+    // step at 2 GPUs against 0.59 without flow mode) take the memory pipeline away from everybody else.
+    while ((int)(ptx::ld_relaxed_sys(f) - value) < 0) {
+      __nanosleep(polls > 32 ? 2048 : (polls > 4 ? 512 : 128));   // GEMM CTAs share this SM: stay out of their issue slots
       if ((++polls & 0xFFu) == 0) {
         const unsigned long long now = ptx::globaltimer_ns();
         if (t0 == 0) t0 = now;
         else if (now - t0 > c.timeout_ns) { atomicAdd(&ws.timeouts, 1u); break; }
       }
     }
+    ptx::fence_acq_rel_sys();   // the one acquire: everything the flag's writer released is visible from here on
   }
   __syncwarp();
 }
@@ -126,12 +137,14 @@ __device__ void flow_forward(const FlowCtx& fc, WaitStats& ws, int lane) {
     }
     __syncwarp();
     if (k == 0 && lane == 0) ws.mark[0] = ptx::globaltimer_ns();
+    flow_stamp(fc, kTraceDoorbell, k, true, lane);
     warp_post_flags(c, kPhaseFlowReady, k, ws.epoch, false, lane);
   }
 }
 
 template <int CODEC, int MODE>
-__device__ void flow_reduce_role(const FlowCtx& fc, WaitStats& ws, uint32_t first, uint32_t step, uint32_t nwarps, int lane) {
+__device__ void flow_reduce_role(const FlowCtx& fc, WaitStats& ws, uint32_t first, uint32_t step, uint32_t nwarps, bool timekeeper,
+                                 int lane) {
   using FC = FrameCodec<CODEC, MODE>;
   const RankCtx& c = fc.c;
   const int N = c.nranks;
@@ -139,6 +152,7 @@ __device__ void flow_reduce_role(const FlowCtx& fc, WaitStats& ws, uint32_t firs
   for (int k = 0; k < fc.nchunks; ++k) {
     const FlowChunk ch = fc.chunk[k];
     warp_wait_flags(c, kPhaseFlowReady, k, ws.epoch, false, lane, ws);
+    flow_stamp(fc, kTraceReduceGo, k, timekeeper, lane);
     const uint32_t shard = flow_shard(ch, N);
     const uint32_t base = ch.frame0 + (uint32_t)c.rank * shard, lim = flow_shard_lim(ch, N, c.rank);
     const uint32_t d_off = ch.d_off;
@@ -156,6 +170,7 @@ __device__ void flow_reduce_role(const FlowCtx& fc, WaitStats& ws, uint32_t firs
       }
       apply_full_w(c, base + j, acc, w, lane);
     });
+    flow_stamp(fc, kTraceReduceDone, k, timekeeper, lane);
     if (N > 1 && warp_ticket_last(c, k, nwarps, lane)) warp_post_flags(c, kPhaseFlowPub, k, ws.epoch, true, lane);
   }
 }
@@ -169,7 +184,9 @@ __device__ void flow_gather_role(const FlowCtx& fc, WaitStats& ws, uint32_t firs
     const FlowChunk ch = fc.chunk[k];
     warp_wait_flags(c, kPhaseFlowPub, k, ws.epoch, true, lane, ws);
     if (timekeeper && k == fc.nchunks - 1 && lane == 0) ws.mark[1] = ptx::globaltimer_ns();
+    flow_stamp(fc, kTraceGatherGo, k, timekeeper, lane);
     gather_stream<CODEC, MODE>(c, flow_shard(ch, c.nranks), ch.frames, first, step, lane, ch.frame0, ch.d_off);
+    flow_stamp(fc, kTraceGatherDone, k, timekeeper, lane);
   }
   if (CODEC == 0) {
     // peers read my gradient in place: nobody may leave (and let the next GEMM overwrite its gradient)
@@ -200,7 +217,8 @@ __device__ __forceinline__ void run_flow(const FlowCtx& fc, int cta, int nctas_t
     if (warp == 0) flow_forward(fc, ws, lane);
   } else {
     const int nr = flow_reduce_warps(c.nranks, wpb), ng = wpb - nr;
-    if (warp < nr) flow_reduce_role<CODEC, MODE>(fc, ws, (uint32_t)(cta * nr + warp), (uint32_t)(workers * nr), (uint32_t)(workers * nr), lane);
+    if (warp < nr) flow_reduce_role<CODEC, MODE>(fc, ws, (uint32_t)(cta * nr + warp), (uint32_t)(workers * nr), (uint32_t)(workers * nr),
+                                                 cta == 0 && warp == 0, lane);
     else flow_gather_role<CODEC, MODE>(fc, ws, (uint32_t)(cta * ng + warp - nr), (uint32_t)(workers * ng), (uint32_t)(workers * ng),
                                        cta == 0 && warp == nr, lane);
   }

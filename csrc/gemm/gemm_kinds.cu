@@ -78,11 +78,25 @@ __device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, 
                : "memory");
 }
 
+// MN-major operands of 32-bit elements cannot use the ordinary 128-byte swizzle (its 16-byte units would
+// keep 4 neighbouring MN elements together where the tensor core needs to transpose single 32-bit
+// values): they use the "128B swizzle, 32-byte atom" mode instead - TMA CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B,
+// descriptor layout type 1 - whose swizzle pattern repeats every 4 rows of 128 bytes (SBO = 512).
+__device__ __forceinline__ uint64_t make_desc_base32(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
+  d |= (uint64_t)1 << 61;  // SWIZZLE_128B_BASE32B
+  return d;
+}
 template <int KIND, bool MN_MAJOR>
 __device__ __forceinline__ uint64_t kind_desc(uint32_t tile_addr, int k) {
   // K-major: 32 bytes further inside the 128-byte row.  MN-major: kUmmaK rows of 128 bytes further; the
   // next 128-byte span along MN starts one TMA box (kBlockK rows x 128 B) later (LBO).
   using T = Kind<KIND>;
+  if constexpr (MN_MAJOR && KIND == KIND_TF32) return make_desc_base32(tile_addr + k * (T::kUmmaK * 128), T::kBlockK * 128, 512);
   return MN_MAJOR ? make_desc(tile_addr + k * (T::kUmmaK * 128), T::kBlockK * 128, 1024) : make_desc(tile_addr + k * 32, 16, 1024);
 }
 
@@ -321,7 +335,8 @@ __global__ void mx_quantize_cols_kernel(const void* x, bool bf16, int K, int col
 
 // ------------------------------------------------------------------------------------------ host
 template <int KIND>
-static int kind_tmap(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_c, uint32_t box_r) {
+static int kind_tmap(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_c, uint32_t box_r,
+                     bool mn_major) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return AINIC_ERR_CUDA;
   constexpr int elem = Kind<KIND>::kElem;
@@ -330,8 +345,9 @@ static int kind_tmap(CUtensorMap* map, const void* base, uint64_t rows, uint64_t
   cuuint32_t box[2] = {box_c, box_r};
   cuuint32_t estr[2] = {1, 1};
   const CUtensorMapDataType dt = KIND == KIND_TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
-  CUresult r = fn(map, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  const CUtensorMapSwizzle sw = (KIND == KIND_TF32 && mn_major) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+  CUresult r = fn(map, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? AINIC_OK : AINIC_ERR_CUDA;
 }
 
@@ -343,11 +359,11 @@ static int launch_kind(const void* a, int lda, const void* b, int ldb, const Epi
   CUtensorMap ta, tb;
   int rc;
   // K-major: global [rows][K], box = kBlockK x rows.  MN-major: global [K][rows], box = one 128-byte span x kBlockK.
-  if (A_MN) rc = kind_tmap<KIND>(&ta, a, ep.K, ep.M, lda, kSpan, T::kBlockK);
-  else rc = kind_tmap<KIND>(&ta, a, ep.M, ep.K, lda, T::kBlockK, BLOCK_M);
+  if (A_MN) rc = kind_tmap<KIND>(&ta, a, ep.K, ep.M, lda, kSpan, T::kBlockK, true);
+  else rc = kind_tmap<KIND>(&ta, a, ep.M, ep.K, lda, T::kBlockK, BLOCK_M, false);
   if (rc) return rc;
-  if (B_MN) rc = kind_tmap<KIND>(&tb, b, ep.K, ep.N, ldb, kSpan, T::kBlockK);
-  else rc = kind_tmap<KIND>(&tb, b, ep.N, ep.K, ldb, T::kBlockK, BLOCK_N);
+  if (B_MN) rc = kind_tmap<KIND>(&tb, b, ep.K, ep.N, ldb, kSpan, T::kBlockK, true);
+  else rc = kind_tmap<KIND>(&tb, b, ep.N, ep.K, ldb, T::kBlockK, BLOCK_N, false);
   if (rc) return rc;
   auto kern = gemm_kind_kernel<KIND, BLOCK_N, A_MN, B_MN, OUT>;
   constexpr int smem = kinds_num_stages(BLOCK_N, KIND) * kinds_stage_bytes(BLOCK_N, KIND) + 1024 + 256;

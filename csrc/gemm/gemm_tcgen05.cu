@@ -176,7 +176,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   }
 
   tc_fence_before();
-  if (ep.done_flag && warp >= 2) __threadfence();   // this thread's output stores, before the CTA-wide barrier
   __syncthreads();
   tc_fence_after();
   if (warp == 1) {
@@ -184,8 +183,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     tmem_dealloc<kTmemCols>(tmem_base);
   }
   if (ep.done_flag && threadIdx.x == 0) {
-    // last-CTA ticket: every CTA's stores are fenced before its increment, so whoever observes the flag
-    // (ld.acquire.gpu in flow.cuh, then the peers it notifies) sees the complete output
+    // last-CTA ticket (the grid-barrier pattern: CTA barrier, then ONE thread fences and takes a ticket - the
+    // barrier orders the epilogue warps' stores before this thread, the fence makes them visible device-wide
+    // before the increment), so whoever observes the flag - ld.acquire.gpu in flow.cuh, then the peers it
+    // notifies - sees the complete output
     __threadfence();
     if (atomicAdd(ep.done_ticket, 1u) == gridDim.x - 1) {
       *ep.done_ticket = 0u;

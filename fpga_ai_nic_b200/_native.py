@@ -171,6 +171,7 @@ def cuda() -> C.CDLL:
     lib.ainic_comm_counters.argtypes = [vp, c_u64p]
     lib.ainic_allreduce_fused.argtypes = [vp, C.POINTER(AllreduceArgs), vp]
     lib.ainic_allreduce_emulate.argtypes = [C.c_int, vp, vp, vp, vp, sz, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+    lib.ainic_comm_flow_trace.argtypes = [vp, c_u64p]
     lib.ainic_allreduce_flow.argtypes = [vp, C.POINTER(AllreduceArgs), C.POINTER(FlowChunk), C.c_int, vp, vp]
     lib.ainic_allreduce_flow_emulate.argtypes = [C.c_int, vp, vp, vp, vp, sz, C.c_float, C.c_int, C.c_int, C.POINTER(sz),
                                                  C.c_int, C.c_int, vp]

@@ -160,6 +160,15 @@ class Communicator:
         return {"busy_ns": out[0], "wait_ns": out[1], "launches": out[2], "timeouts": out[3], "last_ns": out[5],
                 "to_barrier0_ns": out[6], "to_barrier1_ns": out[7]}
 
+    def flow_trace(self, nchunks: int) -> dict:
+        """Per-chunk time line of the last flow call (needs AINIC_FLOW_TRACE=1): microseconds since the first doorbell."""
+        out = (C.c_uint64 * 160)()
+        N.check(self.lib.ainic_comm_flow_trace(self.handle, out), "comm_flow_trace")
+        names = ["doorbell", "reduce_go", "reduce_done", "gather_go", "gather_done"]
+        t0 = min((out[k] for k in range(nchunks) if out[k]), default=0)
+        return {n: [round((out[w * 32 + k] - t0) / 1e3, 1) if out[w * 32 + k] else None for k in range(nchunks)]
+                for w, n in enumerate(names)}
+
     def close(self) -> None:
         if not self._closed:
             self._closed = True

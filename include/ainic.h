@@ -195,6 +195,10 @@ int ainic_allreduce_flow(ainic_comm_t* c, const ainic_allreduce_args_t* args, co
 int ainic_allreduce_flow_emulate(int nranks, float* grads, float* weights, void* weights_bf16, float* grads_out, size_t count,
                                  float lr, int codec, int bfp_mode, const size_t* chunk_counts, int nchunks,
                                  int ctas_per_rank, void* stream);
+/* With AINIC_FLOW_TRACE set, every flow call records %globaltimer stamps per chunk (processing order): out[w * 32 + k],
+ * w = 0 doorbell seen by the forwarder, 1 reduce released, 2 reduce done, 3 gather released, 4 gather done (one
+ * time-keeping warp each).  The software analogue of tapping the FSM states with SignalTap (hw/iochan.stp). */
+int ainic_comm_flow_trace(ainic_comm_t* c, uint64_t out[160]);
 /* Pre-size the communicator's staging for calls of up to `count` values (collective: same call on
  * every rank).  Optional - staging also grows on demand, but growth abandons the old area. */
 int ainic_comm_reserve(ainic_comm_t* c, size_t count);

@@ -89,8 +89,9 @@ def main():
                 dist.all_gather(allsig, sig)
                 same = all(torch.equal(allsig[0], s) for s in allsig)
             loss = float(tr.loss_dev.item()) / cfg.mb
+            trace = tr.comm.flow_trace(cfg.nlayers) if os.environ.get("AINIC_FLOW_TRACE") else None
             res = {"config": spec, "world": world, "best_ms": min(r["ms_per_step"] for r in reps), "reps": reps,
-                   "replicas_identical": same, "loss": loss, "codec": tr.codec}
+                   "replicas_identical": same, "loss": loss, "codec": tr.codec, "flow_trace": trace}
             tr.close()
             tr.comm.close()
         except Exception as ex:  # keep probing

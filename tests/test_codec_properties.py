@@ -17,7 +17,7 @@ def _t(vals, k=0):
     return torch.tensor(vals, dtype=torch.float32) * (2.0 ** k)
 
 
-@settings(max_examples=200, deadline=None)
+@settings(derandomize=True, max_examples=200, deadline=None)
 @given(blocks, scales)
 def test_bfp_clean_error_is_half_a_step_and_requantisation_is_exact(vals, k):
     x = _t(vals, k)
@@ -36,7 +36,7 @@ def test_bfp_clean_error_is_half_a_step_and_requantisation_is_exact(vals, k):
     assert torch.equal(O.bfp_roundtrip(y, O.CLEAN), y)
 
 
-@settings(max_examples=200, deadline=None)
+@settings(derandomize=True, max_examples=200, deadline=None)
 @given(blocks, scales)
 def test_bfp_hw_exact_truncates_toward_minus_infinity(vals, k):
     x = _t(vals, k)
@@ -52,7 +52,7 @@ def test_bfp_hw_exact_truncates_toward_minus_infinity(vals, k):
     assert bool((d > -step * 2.0 ** -16).all()) and bool((d < step * (1 + 2.0 ** -16)).all())
 
 
-@settings(max_examples=100, deadline=None)
+@settings(derandomize=True, max_examples=100, deadline=None)
 @given(st.lists(finite, min_size=32, max_size=32), scales)
 def test_mx_roundtrip_bound_and_fixed_point(vals, k):
     x = _t(vals, k)
@@ -74,7 +74,7 @@ def test_mx_roundtrip_bound_and_fixed_point(vals, k):
     assert torch.equal(O.mx_decompress(buf2, 512)[:32], y)
 
 
-@settings(max_examples=30, deadline=None)
+@settings(derandomize=True, max_examples=30, deadline=None)
 @given(st.integers(min_value=1, max_value=8), st.integers(min_value=1, max_value=3000),
        st.sampled_from(["oneshot", "twoshot"]), st.sampled_from([O.CODEC_BFP, O.CODEC_MXFP8]), st.integers(0, 2 ** 31 - 1))
 def test_fused_allreduce_model_replicas_identical_and_close_to_exact(nranks, count, algo, codec, seed):
@@ -84,12 +84,14 @@ def test_fused_allreduce_model_replicas_identical_and_close_to_exact(nranks, cou
     for r in range(1, nranks):
         assert torch.equal(out[r], out[0])                     # weight replicas cannot drift (SURVEY D11 fixed)
     tol = (0.02 if codec == O.CODEC_BFP else 0.09) * (2 if algo == "twoshot" else 1)
-    denom = exact[0].norm().clamp_min(1e-20)
-    # per-block quantisation noise averages down in the L2 norm; bound it loosely
-    assert ((out[0] - exact[0]).norm() / denom).item() <= tol * np.sqrt(nranks) + 1e-6
+    # The quantisation noise scales with the magnitude of the CONTRIBUTIONS, not of their sum (a handful of
+    # values that nearly cancel would make any bound relative to the exact sum meaningless): measure it
+    # against the norm of all contributions.
+    denom = g.norm().clamp_min(1e-20)
+    assert ((out[0] - exact[0]).norm() / denom).item() <= tol * 1.5 + 1e-6
 
 
-@settings(max_examples=50, deadline=None)
+@settings(derandomize=True, max_examples=50, deadline=None)
 @given(st.integers(min_value=1, max_value=5000), st.floats(min_value=0.0, max_value=1.0, width=32), st.integers(0, 2 ** 31 - 1))
 def test_sgd_is_a_single_fma(count, lr, seed):
     gen = torch.Generator().manual_seed(seed)
