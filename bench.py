@@ -49,7 +49,8 @@ def parse_args():
                     help="--impl ours: skip the PyTorch DDP arms that are otherwise measured in the same invocation")
     ap.add_argument("--no-check", action="store_true", help="skip the replica / update-error checks at N > 1")
     ap.add_argument("--ddp-bucket-mb", type=float, default=34.0, help="bucket_cap_mb of the hardened DDP arm")
-    ap.add_argument("--ddp-mode", default="naive", choices=["naive", "hardened"], help="--impl ddp: which DDP arm")
+    ap.add_argument("--ddp-mode", default="naive", choices=["naive", "hardened", "hardened-eager"],
+                    help="--impl ddp: which DDP arm (hardened-eager = hardened without the CUDA-graph capture)")
     return ap.parse_args()
 
 
@@ -323,7 +324,8 @@ def run_ddp(args, rank, local, world, mode="naive"):
     import torch.nn.functional as F
     dev = torch.device("cuda", local)
     torch.manual_seed(1)
-    hardened = mode == "hardened"
+    hardened = mode in ("hardened", "hardened-eager")
+    try_graph = mode == "hardened"
     pdt = torch.bfloat16 if hardened else torch.float32
     layers = [nn.Linear(args.width, args.width, bias=(args.fuse in (1, 3))) for _ in range(args.layers)]
     seq = []
@@ -375,7 +377,7 @@ def run_ddp(args, rank, local, world, mode="naive"):
 
     graph = None
     graphed = False
-    if hardened:
+    if try_graph:
         try:
             side = torch.cuda.Stream()
             side.wait_stream(torch.cuda.current_stream())
@@ -385,7 +387,9 @@ def run_ddp(args, rank, local, world, mode="naive"):
             torch.cuda.current_stream().wait_stream(side)
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
+            # thread-local capture mode: the NCCL watchdog thread keeps querying events of earlier collectives,
+            # which a global-mode capture treats as an illegal call and invalidates itself on (seen at 8 ranks)
+            with torch.cuda.graph(graph, capture_error_mode="thread_local"):
                 train_step(static_x, static_y)
             graph.replay()
             torch.cuda.synchronize()
@@ -394,12 +398,19 @@ def run_ddp(args, rank, local, world, mode="naive"):
             graph = None
             graph_error = f"{type(ex).__name__}: {str(ex)[:160]}"
             torch.cuda.synchronize()
-    ok = torch.tensor([1 if (graphed or not hardened) else 0], device=dev)
+    ok = torch.tensor([1 if (graphed or not try_graph) else 0], device=dev)
     if world > 1:
         import torch.distributed as dist
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)   # all ranks replay, or none does
-    if hardened and int(ok.item()) == 0:
-        graph, graphed = None, False
+    if try_graph and int(ok.item()) == 0:
+        # a failed capture leaves DDP / NCCL in an undefined state (measured: 5.5 ms/step afterwards): say so and
+        # stop; the caller re-runs this arm as "hardened-eager" in a fresh process
+        if rank == 0:
+            print(json.dumps({"impl": "ddp-hardened", "capture_failed": locals().get("graph_error", "a peer rank could not capture")}), flush=True)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        sys.exit(3)
 
     def step_dev(i):
         if graph is not None:
@@ -480,8 +491,8 @@ def run_ddp(args, rank, local, world, mode="naive"):
         "clocks": {"sm_mhz": clocks.get("sm_mhz"), "sm_max_mhz": clocks.get("sm_max_mhz"), "reasons": clocks.get("reasons", [])},
         "gpu_launches": 0, "loss": loss, "e2e": e2e, "step_ms": step_ms,
     }
-    if hardened and not graphed:
-        out["config"]["cuda_graph_error"] = locals().get("graph_error", "a peer rank could not capture")
+    if mode == "hardened-eager":
+        out["config"]["cuda_graph_error"] = "capture skipped (an attempt in a separate process failed)"
     del model, net, params
     torch.cuda.empty_cache()
     return out
@@ -498,7 +509,11 @@ def measure_baselines(args, ours, rank, world):
         dist.barrier()
     base = {}
     port0 = int(os.environ.get("MASTER_PORT", "29500"))
-    for idx, mode in enumerate(("naive", "hardened")):
+    modes = ["naive", "hardened"]
+    idx = -1
+    while modes:
+        mode = modes.pop(0)
+        idx += 1
         env = dict(os.environ)
         env["MASTER_ADDR"] = "127.0.0.1"
         env["MASTER_PORT"] = str(port0 + 101 + idx)
@@ -522,6 +537,8 @@ def measure_baselines(args, ours, rank, world):
                                   "clocks": d.get("clocks")}
                 else:
                     base[mode] = {"error": f"rc={p.returncode}: {p.stderr[-300:]}"}
+            if mode == "hardened" and p.returncode == 3:
+                modes.append("hardened-eager")       # every rank sees the same exit code: all of them retry
         except Exception as ex:
             base[mode] = {"error": f"{type(ex).__name__}: {str(ex)[:200]}"}
         if world > 1:
@@ -536,7 +553,8 @@ def measure_baselines(args, ours, rank, world):
                                 "product arm (child processes, same GPUs); vs_baseline = value / the faster of the two arms",
                         "ddp": base,
                         "ratio_vs_naive": ours["value"] / ok["naive"]["samples_per_s"] if "naive" in ok else None,
-                        "ratio_vs_hardened": ours["value"] / ok["hardened"]["samples_per_s"] if "hardened" in ok else None,
+                        "ratio_vs_hardened": (ours["value"] / max(ok[m]["samples_per_s"] for m in ("hardened", "hardened-eager") if m in ok))
+                                             if ("hardened" in ok or "hardened-eager" in ok) else None,
                         "e2e_ratio_vs_best": (ours["e2e"]["value"] / best_e2e) if (ours.get("e2e") and best_e2e) else None}}
     if best:
         res["vs_baseline"] = ours["value"] / best
