@@ -70,6 +70,7 @@ def main():
     x = K.cast_bf16((torch.rand(c["mb"], c["width"], generator=gen) * 0.1 - 0.05).cuda())
     y = torch.randint(0, c["width"], (c["mb"],), generator=gen, dtype=torch.int32).cuda()
     finals = {}
+    updates = {}
     for codec in ([c["codec"], "f32"] if world > 1 else ["f32"]):
         cfg = MLPConfig.reference(c["layers"], c["width"], c["mb"])
         cfg.codec = codec
@@ -78,6 +79,15 @@ def main():
         # variance-preserving so that 16 layers of width 16384 stay finite in bf16
         cfg.init_scale = (1.0 / c["width"] ** 0.5) / 0.0289
         tr = MLPTrainer(cfg)
+        # gradient-level accuracy: the update ONE step applies to the last and the first layer, same weights and
+        # batch under both codecs (the reference's disabled check is a per-layer gradient norm,
+        # sw/mlp_mpi_example_f32.cpp:818-826)
+        w0 = {l: tr.buffer("weight", l).clone() for l in (0, c["layers"] - 1)}
+        tr.step(x, y)
+        tr.wait()
+        torch.cuda.synchronize()
+        updates[codec] = {l: tr.buffer("weight", l) - w0[l] for l in w0}
+        del w0
         ms = timed(tr, x, y, a.steps, a.warmup, world)
         res[f"ms_per_step_{codec}"] = ms
         res[f"samples_per_s_{codec}"] = c["mb"] * world / (ms / 1e3)
@@ -97,6 +107,8 @@ def main():
         cfg0 = MLPConfig.reference(c["layers"], c["width"], c["mb"])
         res["weight_rel_l2_err_vs_fp32_allreduce"] = ((wc - wf).norm() / wf.norm()).item()
         res["weight_max_abs_err_vs_fp32_allreduce"] = (wc - wf).abs().max().item()
+        uf, uc = updates["f32"], updates[c["codec"]]
+        res["update_rel_l2_err_vs_fp32_allreduce"] = {f"layer{l}": ((uc[l] - uf[l]).norm() / uf[l].norm().clamp_min(1e-30)).item() for l in uf}
         del cfg0
     if a.t1_ms > 0 or world == 1:
         t1 = a.t1_ms if a.t1_ms > 0 else res["ms_per_step_f32"]
