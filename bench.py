@@ -286,7 +286,7 @@ def run_ours(args, rank, local, world):
         "gpu_launches": int(launches), "e2e": e2e, "loss": loss,
         "gflops_reference_formula": gflops, "comm_counters": ctr, "step_ms": step_ms,
     }
-    out["config"]["flow_mode"] = os.environ.get("AINIC_FLOW", "default (on from 2 ranks)")
+    out["config"]["flow_mode"] = os.environ.get("AINIC_FLOW", "0 (default: one fused all-reduce call per gradient bucket)")
     if world > 1 and not args.no_check:
         try:
             out["correctness"] = check_replicas_and_update(args, tr, cfg, world, rank)

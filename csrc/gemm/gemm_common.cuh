@@ -47,6 +47,9 @@ struct EpiParams {
   // finish bumps *done_flag once every tile of this launch has been stored (release, gpu scope)
   uint32_t* done_flag;
   uint32_t* done_ticket;
+  // plain bf16 / fp32 output of a CTA's LAST tile leaves through shared memory and TMA stores
+  // (epilogue_store_tma); set by the host when no mask / accumulate / doorbell needs per-element access
+  int tma_out;
 };
 
 // Output selector of the epilogue.
@@ -258,14 +261,17 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 // Drain one 128 x BLOCK_N accumulator: thread `lane` of the warp owning TMEM lane quarter q reads
 // row (32 q + lane) 32 columns at a time and writes it with the fused epilogue.
 template <int BLOCK_N, int OUT>
-__device__ __forceinline__ void epilogue_store(const EpiParams& ep, uint32_t taddr, int row, int n0, int half, int nsplit) {
+__device__ __forceinline__ void epilogue_store(const EpiParams& ep, uint32_t taddr, int row, int n0, int half, int nsplit,
+                                               int c_first = 0) {
   constexpr bool OUT_F32 = OUT == OUT_FP32;
   static_assert(OUT != OUT_COMPRESSED || BLOCK_N % 32 == 0, "compressed output works on whole 32-column chunks");
   const bool row_ok = row < ep.M;
   // with 8 epilogue warps two of them share each TMEM lane quarter: `half` 0 drains the first half of the
   // column chunks, `half` 1 the rest; with 4 warps (nsplit == 1) each drains all of them
   constexpr int kChunks = BLOCK_N / 32 + (BLOCK_N % 32 ? 1 : 0);
-  const int c_begin = (nsplit == 2 && half) ? kChunks / 2 : 0, c_end = (nsplit == 2 && !half) ? kChunks / 2 : kChunks;
+  int c_begin = (nsplit == 2 && half) ? kChunks / 2 : 0;
+  const int c_end = (nsplit == 2 && !half) ? kChunks / 2 : kChunks;
+  if (c_begin < c_first) c_begin = c_first;   // the chunks before c_first left through epilogue_store_tma
 #pragma unroll 1
   for (int c = c_begin; c < c_end; ++c) {
     uint32_t r[32];
@@ -351,6 +357,93 @@ __device__ __forceinline__ void epilogue_store(const EpiParams& ep, uint32_t tad
   }
 }
 
+// Epilogue of a CTA's LAST tile through shared memory and TMA stores.  epilogue_store above has every
+// lane write 16 bytes of its own row: 32 rows, 32 half-filled sectors per store instruction - fine
+// while the next tile's main loop hides it, but most GEMMs of the MLP have one tile per CTA, so this
+// drain is exposed.  After the last tile's accumulator is complete the operand ring is idle (every
+// MMA that read it has retired, the producer has nothing left to load), so it becomes the staging
+// area: each epilogue warp parks its 32 rows in 128-byte-wide, 32-row boxes (32 fp32 or 64 bf16
+// columns; 16-byte units XOR-swizzled by row = the SWIZZLE_128B pattern of the output tensor map, and
+// conflict-free for the row-per-lane writes) and one lane hands every finished box to the TMA unit,
+// which writes whole 128-byte lines and clips at the matrix edge.  No box is reused, so nothing
+// waits until the final wait_group.read before the CTA lets go of its shared memory.
+// slab = this TMEM lane quarter's BLOCK_N / box-columns boxes (1024-byte aligned); row0 = first row.
+template <int BLOCK_N, int OUT>
+__device__ __forceinline__ void epilogue_store_tma(const EpiParams& ep, const CUtensorMap* tmap_c, uint32_t taddr, int row0,
+                                                   int n0, uint8_t* slab, int lane, int half, int nsplit) {
+  static_assert(OUT == OUT_BF16 || OUT == OUT_FP32, "plain outputs only");
+  constexpr bool F32 = OUT == OUT_FP32;
+  constexpr int kCPB = F32 ? 1 : 2;              // 32-column accumulator chunks per box
+  constexpr int kBoxCols = 32 * kCPB;
+  constexpr int kBoxes = BLOCK_N / kBoxCols;     // a 16-column remainder (BLOCK_N = 208) goes out directly
+  const int c_begin = ((nsplit == 2 && half) ? kBoxes / 2 : 0) * kCPB;
+  const int c_end = ((nsplit == 2 && !half) ? kBoxes / 2 : kBoxes) * kCPB;
+  const uint32_t sw = (uint32_t)(lane & 7);
+  auto process = [&](const uint32_t (&r)[32], int c) {
+    const int b = c / kCPB;
+    uint8_t* box = slab + b * 4096;
+    uint4* srow = reinterpret_cast<uint4*>(box + lane * 128);
+    const int col0 = n0 + c * 32;
+    if constexpr (F32) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        uint4 o;
+        o.x = __float_as_uint(__uint_as_float(r[4 * u]) * ep.alpha);
+        o.y = __float_as_uint(__uint_as_float(r[4 * u + 1]) * ep.alpha);
+        o.z = __float_as_uint(__uint_as_float(r[4 * u + 2]) * ep.alpha);
+        o.w = __float_as_uint(__uint_as_float(r[4 * u + 3]) * ep.alpha);
+        srow[(uint32_t)u ^ sw] = o;
+      }
+    } else {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
+        if (ep.bias && col0 + g * 8 < ep.N) {
+          const float4 b0 = *reinterpret_cast<const float4*>(ep.bias + col0 + g * 8);
+          const float4 b1 = *reinterpret_cast<const float4*>(ep.bias + col0 + g * 8 + 4);
+          v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+          v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+        }
+        if (ep.relu) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.0f);
+        }
+        uint4 o;
+        o.x = pack_bf16(v[0], v[1]);
+        o.y = pack_bf16(v[2], v[3]);
+        o.z = pack_bf16(v[4], v[5]);
+        o.w = pack_bf16(v[6], v[7]);
+        srow[(uint32_t)((c & 1) * 4 + g) ^ sw] = o;
+      }
+    }
+    if (c % kCPB == kCPB - 1) {   // box complete: generic-proxy writes -> async proxy, then one lane issues the store
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0 && row0 < ep.M && n0 + b * kBoxCols < ep.N) tma_store_2d(tmap_c, box, n0 + b * kBoxCols, row0);
+    }
+  };
+  // the TMEM read of the next chunk is in flight while this one is converted and parked
+  uint32_t ra[32], rb[32];
+  if (c_begin < c_end) tmem_ld_32x32b_x32(taddr + c_begin * 32, ra);
+#pragma unroll 1
+  for (int c = c_begin; c < c_end; c += 2) {
+    tmem_ld_wait();
+    if (c + 1 < c_end) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, rb);
+    process(ra, c);
+    if (c + 1 < c_end) {
+      tmem_ld_wait();
+      if (c + 2 < c_end) tmem_ld_32x32b_x32(taddr + (c + 2) * 32, ra);
+      process(rb, c + 1);
+    }
+  }
+  if (lane == 0) tma_store_commit();
+  if constexpr (BLOCK_N % kBoxCols != 0) epilogue_store<BLOCK_N, OUT>(ep, taddr, row0 + lane, n0, half, nsplit, kBoxes * kCPB);
+  if (lane == 0) tma_store_wait_read<0>();
+  __syncwarp();
+}
+
 // ------------------------------------------------------------------------------------------ host
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -371,14 +464,14 @@ inline EncodeTiledFn get_encode_fn() {
 
 // bf16 row-major [rows][cols] (cols contiguous, leading dimension ld elements); box = box_c x box_r.
 inline int make_tmap(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_c,
-                     uint32_t box_r) {
+                     uint32_t box_r, bool f32 = false) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return AINIC_ERR_CUDA;
   cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstride[1] = {ld * 2};
+  cuuint64_t gstride[1] = {ld * (f32 ? 4 : 2)};
   cuuint32_t box[2] = {box_c, box_r};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+  CUresult r = fn(map, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? AINIC_OK : AINIC_ERR_CUDA;
@@ -390,21 +483,23 @@ struct TmapKey {
   const void* base;
   uint64_t rows, cols, ld;
   uint32_t box_c, box_r;
+  bool f32;
   bool operator==(const TmapKey& o) const {
-    return base == o.base && rows == o.rows && cols == o.cols && ld == o.ld && box_c == o.box_c && box_r == o.box_r;
+    return base == o.base && rows == o.rows && cols == o.cols && ld == o.ld && box_c == o.box_c && box_r == o.box_r && f32 == o.f32;
   }
 };
 inline int cached_tmap(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_c,
-                       uint32_t box_r) {
+                       uint32_t box_r, bool f32 = false) {
   constexpr int kSlots = 256;
   struct Slot { TmapKey key; CUtensorMap map; bool valid; };
   static thread_local Slot slots[kSlots];
-  const TmapKey key{base, rows, cols, ld, box_c, box_r};
+  const TmapKey key{base, rows, cols, ld, box_c, box_r, f32};
   uint64_t h = reinterpret_cast<uint64_t>(base) >> 8;
+  h ^= (uint64_t)f32 << 40;
   h ^= rows * 0x9E3779B97F4A7C15ull ^ cols * 0xC2B2AE3D27D4EB4Full ^ (uint64_t)box_r * 0x165667B19E3779F9ull ^ ld << 17 ^ box_c;
   Slot& s = slots[(h ^ (h >> 29)) % kSlots];
   if (!(s.valid && s.key == key)) {
-    const int rc = make_tmap(&s.map, base, rows, cols, ld, box_c, box_r);
+    const int rc = make_tmap(&s.map, base, rows, cols, ld, box_c, box_r, f32);
     if (rc) { s.valid = false; return rc; }
     s.key = key;
     s.valid = true;
@@ -433,6 +528,13 @@ inline int gemm_threads() {
 inline int gemm_epi_sleep_ns() {
   static const int v = getenv("AINIC_GEMM_EPI_SLEEP") ? atoi(getenv("AINIC_GEMM_EPI_SLEEP")) : 0;
   return v;
+}
+
+// Last-tile epilogue through shared memory + TMA stores (epilogue_store_tma); AINIC_GEMM_TMA_STORE=0 keeps
+// the direct row-per-lane stores everywhere.
+inline bool tma_store_enabled() {
+  static const bool on = !(getenv("AINIC_GEMM_TMA_STORE") && atoi(getenv("AINIC_GEMM_TMA_STORE")) == 0);
+  return on;
 }
 
 inline bool pdl_enabled() {

@@ -12,7 +12,8 @@
 // when the shape allows it.  Structure of both: persistent, warp-specialised, one CTA per SM.
 //   warp 0   : TMA producer (one elected lane)         global -> 128B-swizzled smem ring
 //   warp 1   : TMEM allocator + MMA issuer (one lane)  tcgen05.mma kind::f16
-//   warps 2-5: epilogue                                tcgen05.ld 32x32b -> registers -> global
+//   warps 2-5: epilogue                                tcgen05.ld 32x32b -> registers -> global (a CTA's last
+//              tile: -> the idle operand ring -> TMA stores, epilogue_store_tma)
 // Two TMEM accumulator stages let the epilogue of tile i overlap the main loop of tile i+1; the
 // prologue overlaps the previous kernel's tail through programmatic dependent launch.
 #include <stdio.h>
@@ -38,7 +39,8 @@ __host__ __device__ constexpr uint32_t tmem_cols(int block_n) {
 
 template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
 __global__ void __launch_bounds__(kThreads, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, EpiParams ep) {
+gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+            const __grid_constant__ CUtensorMap tmap_c, EpiParams ep) {
   constexpr int kStages = num_stages(BLOCK_N);
   constexpr int kABytes = BLOCK_M * BLOCK_K * 2;
   constexpr int kBBytes = BLOCK_N * BLOCK_K * 2;
@@ -69,6 +71,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
+    if (ep.tma_out) tma_prefetch_desc(&tmap_c);
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -165,6 +168,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         } else {
           epilogue_store<BLOCK_N, OUT_COMPRESSED>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
         }
+      } else if constexpr (OUT_F32 == OUT_BF16 || OUT_F32 == OUT_FP32) {
+        if (ep.tma_out && tile + (int)gridDim.x >= num_tiles) {
+          // last tile of this CTA: the operand ring is idle, stage through it and let the TMA unit write
+          constexpr int kSlab = (BLOCK_N / (OUT_F32 == OUT_FP32 ? 32 : 64)) * 4096;
+          static_assert(4 * kSlab <= kStages * (kABytes + kBBytes), "staging boxes must fit in the operand ring");
+          epilogue_store_tma<BLOCK_N, OUT_F32>(ep, &tmap_c, taddr, m0 + quarter * 32, n0, smem + quarter * kSlab, lane, warp >= 6,
+                                               epi_warps / 4);
+        } else {
+          epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
+        }
       } else {
         epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
       }
@@ -199,7 +212,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
 template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
 static int launch(const void* a, int lda, const void* b, int ldb, const EpiParams& ep, int max_ctas,
                   cudaStream_t stream) {
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tc;
   int rc;
   // A: K-major -> global [M][K]; MN-major -> global [K][M].
   if (A_MN) rc = cached_tmap(&ta, a, ep.K, ep.M, lda, 64, BLOCK_K);
@@ -207,6 +220,10 @@ static int launch(const void* a, int lda, const void* b, int ldb, const EpiParam
   if (rc) return rc;
   if (B_MN) rc = cached_tmap(&tb, b, ep.K, ep.N, ldb, 64, BLOCK_K);
   else rc = cached_tmap(&tb, b, ep.N, ep.K, ldb, BLOCK_K, BLOCK_N);
+  if (rc) return rc;
+  // output map of the TMA-store epilogue: 128-byte-wide, 32-row boxes (one per epilogue warp and column group)
+  if (ep.tma_out) rc = cached_tmap(&tc, ep.c, ep.M, ep.N, ep.ldc, OUT_F32 == OUT_FP32 ? 32 : 64, 32, OUT_F32 == OUT_FP32);
+  else tc = ta;
   if (rc) return rc;
   auto kern = gemm_kernel<BLOCK_N, A_MN, B_MN, OUT_F32>;
   constexpr int smem = num_stages(BLOCK_N) * stage_bytes(BLOCK_N) + 1024 + 256 + staging_bytes(BLOCK_N, OUT_F32);
@@ -230,7 +247,7 @@ static int launch(const void* a, int lda, const void* b, int ldb, const EpiParam
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  if (cudaLaunchKernelEx(&cfg, kern, ta, tb, ep) != cudaSuccess) return AINIC_ERR_CUDA;
+  if (cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, ep) != cudaSuccess) return AINIC_ERR_CUDA;
   return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
 }
 
@@ -303,6 +320,8 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
     static const int stage_env = getenv("AINIC_GEMM_STAGE_FRAMES") ? atoi(getenv("AINIC_GEMM_STAGE_FRAMES")) : -1;
     ep.stage_frames = stage_env >= 0 ? stage_env : (ep.push_n > 1 ? 1 : 0);
   }
+  ep.tma_out = tma_store_enabled() && c && !ep.cgrad && !ep.accumulate && !ep.mask_out && !ep.mask_in && !ep.done_flag &&
+               ((uintptr_t)c & 15) == 0 && (layout != AINIC_GEMM_TN || (ldc % 4) == 0);
   if (ep.cgrad) {  // compressed gradient output: backward-weight layout only, whole 32-value groups
     if (layout != AINIC_GEMM_TN || (N % 32) || (ldc % 32) || ((uintptr_t)ep.cgrad & 15) ||
         (ep.codec != AINIC_CODEC_BFP && ep.codec != AINIC_CODEC_MXFP8))
