@@ -379,11 +379,18 @@ __device__ __forceinline__ void epilogue_store_tma(const EpiParams& ep, const CU
   const int c_begin = ((nsplit == 2 && half) ? kBoxes / 2 : 0) * kCPB;
   const int c_end = ((nsplit == 2 && !half) ? kBoxes / 2 : kBoxes) * kCPB;
   const uint32_t sw = (uint32_t)(lane & 7);
-  auto process = [&](const uint32_t (&r)[32], int c) {
+  // One 32-register buffer: the TMEM read of chunk c + 1 is issued as soon as chunk c's values have been
+  // handed to the st.shared instructions, so it overlaps the fence and the TMA issue.  (Two buffers cost
+  // 80 more registers per thread - enough to stop an all-reduce CTA from sharing the SM with this one.)
+  uint32_t r[32];
+  if (c_begin < c_end) tmem_ld_32x32b_x32(taddr + c_begin * 32, r);
+#pragma unroll 1
+  for (int c = c_begin; c < c_end; ++c) {
     const int b = c / kCPB;
     uint8_t* box = slab + b * 4096;
     uint4* srow = reinterpret_cast<uint4*>(box + lane * 128);
     const int col0 = n0 + c * 32;
+    tmem_ld_wait();
     if constexpr (F32) {
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
@@ -418,24 +425,11 @@ __device__ __forceinline__ void epilogue_store_tma(const EpiParams& ep, const CU
         srow[(uint32_t)((c & 1) * 4 + g) ^ sw] = o;
       }
     }
+    if (c + 1 < c_end) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, r);
     if (c % kCPB == kCPB - 1) {   // box complete: generic-proxy writes -> async proxy, then one lane issues the store
       fence_proxy_async();
       __syncwarp();
       if (lane == 0 && row0 < ep.M && n0 + b * kBoxCols < ep.N) tma_store_2d(tmap_c, box, n0 + b * kBoxCols, row0);
-    }
-  };
-  // the TMEM read of the next chunk is in flight while this one is converted and parked
-  uint32_t ra[32], rb[32];
-  if (c_begin < c_end) tmem_ld_32x32b_x32(taddr + c_begin * 32, ra);
-#pragma unroll 1
-  for (int c = c_begin; c < c_end; c += 2) {
-    tmem_ld_wait();
-    if (c + 1 < c_end) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, rb);
-    process(ra, c);
-    if (c + 1 < c_end) {
-      tmem_ld_wait();
-      if (c + 2 < c_end) tmem_ld_32x32b_x32(taddr + (c + 2) * 32, ra);
-      process(rb, c + 1);
     }
   }
   if (lane == 0) tma_store_commit();

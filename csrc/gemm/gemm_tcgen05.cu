@@ -37,8 +37,11 @@ __host__ __device__ constexpr uint32_t tmem_cols(int block_n) {
   return 2 * block_n <= 32 ? 32u : 2 * block_n <= 64 ? 64u : 2 * block_n <= 128 ? 128u : 2 * block_n <= 256 ? 256u : 512u;
 }
 
+// Register cap (min-blocks 2 of 320 threads = 102 registers): one CTA per SM runs (shared memory), but an
+// all-reduce CTA must fit beside it - 256 threads x 144 registers (overlap kernels) or x 168 (flow kernel)
+// leave 28.6 K / 22.5 K of the SM's 64 K registers for this kernel's 192 threads.
 template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 2)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
             const __grid_constant__ CUtensorMap tmap_c, EpiParams ep) {
   constexpr int kStages = num_stages(BLOCK_N);
