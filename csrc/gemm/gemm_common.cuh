@@ -50,6 +50,9 @@ struct EpiParams {
   // plain bf16 / fp32 output of a CTA's LAST tile leaves through shared memory and TMA stores
   // (epilogue_store_tma); set by the host when no mask / accumulate / doorbell needs per-element access
   int tma_out;
+  // diagnostics (ainic_gemm_trace): 8 time stamps per CTA - entry, after griddepcontrol.wait, first operand
+  // stage landed, last MMA issued, first accumulator complete, epilogue done, exit; null = off
+  unsigned long long* trace;
 };
 
 // Output selector of the epilogue.
@@ -373,37 +376,32 @@ __device__ __forceinline__ void epilogue_store_tma(const EpiParams& ep, const CU
                                                    int n0, uint8_t* slab, int lane, int half, int nsplit) {
   static_assert(OUT == OUT_BF16 || OUT == OUT_FP32, "plain outputs only");
   constexpr bool F32 = OUT == OUT_FP32;
-  constexpr int kCPB = F32 ? 1 : 2;              // 32-column accumulator chunks per box
-  constexpr int kBoxCols = 32 * kCPB;
+  constexpr int kCPB = F32 ? 2 : 4;              // 16-column accumulator chunks per box
+  constexpr int kBoxCols = 16 * kCPB;
   constexpr int kBoxes = BLOCK_N / kBoxCols;     // a 16-column remainder (BLOCK_N = 208) goes out directly
   const int c_begin = ((nsplit == 2 && half) ? kBoxes / 2 : 0) * kCPB;
   const int c_end = ((nsplit == 2 && !half) ? kBoxes / 2 : kBoxes) * kCPB;
   const uint32_t sw = (uint32_t)(lane & 7);
-  // One 32-register buffer: the TMEM read of chunk c + 1 is issued as soon as chunk c's values have been
-  // handed to the st.shared instructions, so it overlaps the fence and the TMA issue.  (Two buffers cost
-  // 80 more registers per thread - enough to stop an all-reduce CTA from sharing the SM with this one.)
-  uint32_t r[32];
-  if (c_begin < c_end) tmem_ld_32x32b_x32(taddr + c_begin * 32, r);
-#pragma unroll 1
-  for (int c = c_begin; c < c_end; ++c) {
+  // one 16-column chunk of this lane's row: convert, park its two (bf16) / four (fp32) 16-byte units; when
+  // it completes a box: generic-proxy writes -> async proxy, then one lane hands the box to the TMA unit
+  auto park = [&](const uint32_t (&r)[16], int c) {
     const int b = c / kCPB;
     uint8_t* box = slab + b * 4096;
     uint4* srow = reinterpret_cast<uint4*>(box + lane * 128);
-    const int col0 = n0 + c * 32;
-    tmem_ld_wait();
     if constexpr (F32) {
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
+      for (int u = 0; u < 4; ++u) {
         uint4 o;
         o.x = __float_as_uint(__uint_as_float(r[4 * u]) * ep.alpha);
         o.y = __float_as_uint(__uint_as_float(r[4 * u + 1]) * ep.alpha);
         o.z = __float_as_uint(__uint_as_float(r[4 * u + 2]) * ep.alpha);
         o.w = __float_as_uint(__uint_as_float(r[4 * u + 3]) * ep.alpha);
-        srow[(uint32_t)u ^ sw] = o;
+        srow[(uint32_t)((c % kCPB) * 4 + u) ^ sw] = o;
       }
     } else {
+      const int col0 = n0 + c * 16;
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
+      for (int g = 0; g < 2; ++g) {
         float v[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g * 8 + j]);
@@ -422,18 +420,31 @@ __device__ __forceinline__ void epilogue_store_tma(const EpiParams& ep, const CU
         o.y = pack_bf16(v[2], v[3]);
         o.z = pack_bf16(v[4], v[5]);
         o.w = pack_bf16(v[6], v[7]);
-        srow[(uint32_t)((c & 1) * 4 + g) ^ sw] = o;
+        srow[(uint32_t)((c % kCPB) * 2 + g) ^ sw] = o;
       }
     }
-    if (c + 1 < c_end) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, r);
-    if (c % kCPB == kCPB - 1) {   // box complete: generic-proxy writes -> async proxy, then one lane issues the store
+    if (c % kCPB == kCPB - 1) {
       fence_proxy_async();
       __syncwarp();
       if (lane == 0 && row0 < ep.M && n0 + b * kBoxCols < ep.N) tma_store_2d(tmap_c, box, n0 + b * kBoxCols, row0);
     }
+  };
+  // Two 16-register buffers: the TMEM read of the next chunk is in flight while this one is converted and
+  // parked.  (With 32-column chunks the second buffer costs enough registers to stop an all-reduce CTA from
+  // sharing the SM with this one; without a second buffer the bf16 epilogue is ~1 us slower.)
+  uint32_t ra[16], rb[16];
+  if (c_begin < c_end) tmem_ld_32x32b_x16(taddr + c_begin * 16, ra);
+#pragma unroll 1
+  for (int c = c_begin; c < c_end; c += 2) {   // chunk counts per warp are even
+    tmem_ld_wait();
+    tmem_ld_32x32b_x16(taddr + (c + 1) * 16, rb);
+    park(ra, c);
+    tmem_ld_wait();
+    if (c + 2 < c_end) tmem_ld_32x32b_x16(taddr + (c + 2) * 16, ra);
+    park(rb, c + 1);
   }
   if (lane == 0) tma_store_commit();
-  if constexpr (BLOCK_N % kBoxCols != 0) epilogue_store<BLOCK_N, OUT>(ep, taddr, row0 + lane, n0, half, nsplit, kBoxes * kCPB);
+  if constexpr (BLOCK_N % kBoxCols != 0) epilogue_store<BLOCK_N, OUT>(ep, taddr, row0 + lane, n0, half, nsplit, kBoxes * kBoxCols / 32);
   if (lane == 0) tma_store_wait_read<0>();
   __syncwarp();
 }

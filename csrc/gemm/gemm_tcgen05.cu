@@ -65,6 +65,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int epi_warps = (int)(blockDim.x >> 5) - 2;   // 4 or 8 (two per TMEM lane quarter)
+  unsigned long long* const trace = ep.trace ? ep.trace + (size_t)blockIdx.x * 8 : nullptr;
+  if (trace && threadIdx.x == 0) trace[0] = globaltimer_ns();
 
   const int m_tiles = (ep.M + BLOCK_M - 1) / BLOCK_M;
   const int n_tiles = (ep.N + BLOCK_N - 1) / BLOCK_N;
@@ -95,6 +97,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   // it may have written.
   griddep_wait();
   griddep_launch_dependents();
+  if (trace && threadIdx.x == 0) trace[1] = globaltimer_ns();
 
   if (warp == 0) {
     // ===================================================== TMA producer
@@ -141,6 +144,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
+          if (trace && kb == 0 && tile == (int)blockIdx.x) trace[2] = globaltimer_ns();
           const uint32_t a_addr = smem_u32(smem_a + stage * kABytes);
           const uint32_t b_addr = smem_u32(smem_b + stage * kBBytes);
 #pragma unroll
@@ -152,6 +156,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
+      if (trace) trace[3] = globaltimer_ns();
     }
   } else {
     // ===================================================== epilogue (warps 2..5)
@@ -163,6 +168,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       const int n0 = (tile / m_tiles) * BLOCK_N;
       mbar_wait_backoff(&tmem_full[acc], acc_phase, (uint32_t)ep.epi_sleep);
       tc_fence_after();
+      if (trace && warp == 2 && lane == 0 && tile == (int)blockIdx.x) trace[4] = globaltimer_ns();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N);
       if constexpr (staged_frames(BLOCK_N, OUT_F32)) {
         if (epi_warps == 4) {   // compressed frames leave through shared memory, whole row segments at a time
@@ -189,6 +195,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
+    if (trace && warp == 2 && lane == 0) trace[5] = globaltimer_ns();
   }
 
   tc_fence_before();
@@ -198,6 +205,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     __syncwarp();
     tmem_dealloc<kTmemCols>(tmem_base);
   }
+  if (trace && threadIdx.x == 0) trace[6] = globaltimer_ns();
   if (ep.done_flag && threadIdx.x == 0) {
     // last-CTA ticket (the grid-barrier pattern: CTA barrier, then ONE thread fences and takes a ticket - the
     // barrier orders the epilogue warps' stores before this thread, the fence makes them visible device-wide
@@ -211,6 +219,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
     }
   }
 }
+
+// ainic_gemm_trace state: the next `left` launches of the 1-CTA kernel write their per-CTA time stamps to
+// consecutive [148][8] blocks of `buf` (diagnostics, scripts/gemm_timeline.py).
+static unsigned long long* g_trace_buf = nullptr;
+static int g_trace_left = 0;
 
 template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
 static int launch(const void* a, int lda, const void* b, int ldb, const EpiParams& ep, int max_ctas,
@@ -250,7 +263,13 @@ static int launch(const void* a, int lda, const void* b, int ldb, const EpiParam
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  if (cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, ep) != cudaSuccess) return AINIC_ERR_CUDA;
+  EpiParams e2 = ep;
+  if (g_trace_left > 0) {
+    e2.trace = g_trace_buf;
+    g_trace_buf += 148 * 8;
+    --g_trace_left;
+  }
+  if (cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, e2) != cudaSuccess) return AINIC_ERR_CUDA;
   return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
 }
 
@@ -271,6 +290,12 @@ using namespace ainic::gemm;
 #define DISPATCH_BN(BN, AMN, BMN, F32)                                                     \
   case BN:                                                                                 \
     return launch<BN, AMN, BMN, F32>(a, lda, b, ldb, ep, max_ctas, (cudaStream_t)stream);
+
+extern "C" int ainic_gemm_trace(void* buf, int launches) {
+  g_trace_buf = static_cast<unsigned long long*>(buf);
+  g_trace_left = buf ? launches : 0;
+  return AINIC_OK;
+}
 
 // block_n: 0 = choose; > 0 = 1-CTA kernel with that tile width; < 0 = 2-CTA kernel with width -block_n.
 extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b, int ldb, void* c, int ldc, int M,

@@ -150,6 +150,7 @@ def cuda() -> C.CDLL:
     lib.ainic_cast_f32_bf16.argtypes = [vp, vp, sz, vp]
     lib.ainic_gemm_bf16.argtypes = [C.c_int, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.POINTER(GemmEpilogue), C.c_int, C.c_int, vp]
+    lib.ainic_gemm_trace.argtypes = [vp, C.c_int]
     lib.ainic_gemm_tf32.argtypes = [C.c_int, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.POINTER(GemmEpilogue), C.c_int, C.c_int, vp]
     lib.ainic_mx_sf_bytes.restype = sz

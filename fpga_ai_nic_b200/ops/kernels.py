@@ -266,6 +266,14 @@ def allreduce_flow_emulate(grads: torch.Tensor, weights: torch.Tensor | None, lr
     return gout, weights, shadow
 
 
+def gemm_trace(buf: torch.Tensor | None, launches: int = 0) -> None:
+    """Diagnostics (ainic_gemm_trace): the next ``launches`` bf16 GEMM launches write per-CTA time stamps into
+    ``buf`` (int64, ``[launches, 148, 8]``, zero-filled by the caller); ``None`` switches it off."""
+    if buf is not None:
+        assert buf.dtype == torch.int64 and buf.is_cuda and buf.is_contiguous() and buf.numel() >= launches * 148 * 8
+    N.check(N.cuda().ainic_gemm_trace(buf.data_ptr() if buf is not None else None, int(launches)), "gemm_trace")
+
+
 # ---------------------------------------------------------------- tf32 and MX block-scaled GEMMs (csrc/gemm/gemm_kinds.cu)
 def gemm_tf32(layout: int, a: torch.Tensor, b: torch.Tensor, out: torch.Tensor | None = None, alpha: float = 1.0,
               accumulate: bool = False, block_n: int = 0, max_ctas: int = 0) -> torch.Tensor:

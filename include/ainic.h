@@ -98,6 +98,12 @@ typedef struct ainic_gemm_epilogue {
 int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b, int ldb, void* c, int ldc, int M, int N,
                     int K, const ainic_gemm_epilogue_t* epi, int block_n, int max_ctas, void* stream);
 
+/* Diagnostics: the next `launches` launches of the 1-CTA bf16 kernel write seven time stamps per CTA
+ * (%globaltimer ns: entry, after griddepcontrol.wait, first operand stage landed, last MMA issued, first
+ * accumulator complete, epilogue done, exit) into consecutive [148][8] uint64 blocks of the device buffer
+ * `buf`; buf = NULL switches it off.  Not thread safe; scripts/gemm_timeline.py. */
+int ainic_gemm_trace(void* buf, int launches);
+
 /* fp32 operands on the tensor cores as tf32 (tcgen05.mma.kind::tf32), fp32 result with the alpha / accumulate
  * epilogue; layouts as ainic_gemm_bf16.  The tensor-core form of the reference's all-fp32 MLP
  * (libxsmm_dnn_fc_*_exec_f32, sw/mlp_mpi_example_f32.cpp:708-709, :741-742): no bf16 rounding anywhere.
