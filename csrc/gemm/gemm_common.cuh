@@ -542,6 +542,22 @@ inline bool tma_store_enabled() {
   return on;
 }
 
+// ainic_gemm_trace state: the next `left` launches write their per-CTA time stamps to consecutive [148][8]
+// blocks of `buf` (diagnostics, scripts/gemm_timeline.py).  One instance for both kernel files.
+struct TraceState { unsigned long long* buf = nullptr; int left = 0; };
+inline TraceState& trace_state() {
+  static TraceState t;
+  return t;
+}
+inline void trace_attach(EpiParams& ep) {
+  TraceState& t = trace_state();
+  if (t.left > 0) {
+    ep.trace = t.buf;
+    t.buf += 148 * 8;
+    --t.left;
+  }
+}
+
 inline bool pdl_enabled() {
   static const bool on = !(getenv("AINIC_GEMM_PDL") && atoi(getenv("AINIC_GEMM_PDL")) == 0);
   return on;

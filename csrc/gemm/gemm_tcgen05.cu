@@ -37,11 +37,13 @@ __host__ __device__ constexpr uint32_t tmem_cols(int block_n) {
   return 2 * block_n <= 32 ? 32u : 2 * block_n <= 64 ? 64u : 2 * block_n <= 128 ? 128u : 2 * block_n <= 256 ? 256u : 512u;
 }
 
-// Register cap (min-blocks 2 of 320 threads = 102 registers): one CTA per SM runs (shared memory), but an
-// all-reduce CTA must fit beside it - 256 threads x 144 registers (overlap kernels) or x 168 (flow kernel)
-// leave 28.6 K / 22.5 K of the SM's 64 K registers for this kernel's 192 threads.
+// Register cap: one CTA per SM runs (shared memory), but an all-reduce CTA must fit beside it, and registers
+// are allocated per SM sub-partition (16 K each): the all-reduce CTA's 8 warps put two on each sub-partition
+// (2 x 32 x 144 registers for the overlap kernels, x 168 for the flow kernel), this kernel's 6 warps up to
+// two more, which leaves 112 / 88 registers per thread.  With 96 the flow kernel's doorbells were never
+// rung: the GEMM CTAs could not become resident beside it.
 template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __maxnreg__(88)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
             const __grid_constant__ CUtensorMap tmap_c, EpiParams ep) {
   constexpr int kStages = num_stages(BLOCK_N);
@@ -220,11 +222,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   }
 }
 
-// ainic_gemm_trace state: the next `left` launches of the 1-CTA kernel write their per-CTA time stamps to
-// consecutive [148][8] blocks of `buf` (diagnostics, scripts/gemm_timeline.py).
-static unsigned long long* g_trace_buf = nullptr;
-static int g_trace_left = 0;
-
 template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
 static int launch(const void* a, int lda, const void* b, int ldb, const EpiParams& ep, int max_ctas,
                   cudaStream_t stream) {
@@ -264,11 +261,7 @@ static int launch(const void* a, int lda, const void* b, int ldb, const EpiParam
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
   EpiParams e2 = ep;
-  if (g_trace_left > 0) {
-    e2.trace = g_trace_buf;
-    g_trace_buf += 148 * 8;
-    --g_trace_left;
-  }
+  trace_attach(e2);
   if (cudaLaunchKernelEx(&cfg, kern, ta, tb, tc, e2) != cudaSuccess) return AINIC_ERR_CUDA;
   return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
 }
@@ -292,8 +285,8 @@ using namespace ainic::gemm;
     return launch<BN, AMN, BMN, F32>(a, lda, b, ldb, ep, max_ctas, (cudaStream_t)stream);
 
 extern "C" int ainic_gemm_trace(void* buf, int launches) {
-  g_trace_buf = static_cast<unsigned long long*>(buf);
-  g_trace_left = buf ? launches : 0;
+  trace_state().buf = static_cast<unsigned long long*>(buf);
+  trace_state().left = buf ? launches : 0;
   return AINIC_OK;
 }
 

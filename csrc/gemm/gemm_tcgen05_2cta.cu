@@ -52,6 +52,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   const bool leader = cta_rank == 0;
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
+  unsigned long long* const trace = ep.trace ? ep.trace + (size_t)blockIdx.x * 8 : nullptr;
+  if (trace && threadIdx.x == 0) trace[0] = globaltimer_ns();
 
   const int m_tiles = (ep.M + 2 * BLOCK_M - 1) / (2 * BLOCK_M);
   const int n_tiles = (ep.N + BLOCK_N - 1) / BLOCK_N;
@@ -78,6 +80,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   const uint32_t tmem_base = *tmem_ptr;
   griddep_wait();
   griddep_launch_dependents();
+  if (trace && threadIdx.x == 0) trace[1] = globaltimer_ns();
 
   if (warp == 0) {
     // ===================================================== TMA producer (both CTAs)
@@ -130,6 +133,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
+          if (trace && kb == 0 && tile == cluster_id) trace[2] = globaltimer_ns();
           const uint32_t a_addr = smem_u32(smem_a + stage * kABytes);
           const uint32_t b_addr = smem_u32(smem_b + stage * kBBytes);
 #pragma unroll
@@ -141,6 +145,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
+      if (trace) trace[3] = globaltimer_ns();
     }
   } else {
     // ===================================================== epilogue (warps 2..5, both CTAs)
@@ -152,6 +157,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       const int n0 = (tile / m_tiles) * BLOCK_N;
       mbar_wait_backoff(&tmem_full[acc], acc_phase, (uint32_t)ep.epi_sleep);
       tc_fence_after();
+      if (trace && warp == 2 && lane == 0 && tile == cluster_id) trace[4] = globaltimer_ns();
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N);
       epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
       tc_fence_before();
@@ -162,6 +168,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
+    if (trace && warp == 2 && lane == 0) trace[5] = globaltimer_ns();
   }
 
   tc_fence_before();
@@ -171,6 +178,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
     __syncwarp();
     tmem_dealloc_2cta<kTmemCols>(tmem_base);
   }
+  if (trace && threadIdx.x == 0) trace[6] = globaltimer_ns();
 }
 
 template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
@@ -211,7 +219,9 @@ static int launch2(const void* a, int lda, const void* b, int ldb, const EpiPara
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
-  if (cudaLaunchKernelEx(&cfg, kern, ta, tb, ep) != cudaSuccess) return AINIC_ERR_CUDA;
+  EpiParams e2 = ep;
+  trace_attach(e2);
+  if (cudaLaunchKernelEx(&cfg, kern, ta, tb, e2) != cudaSuccess) return AINIC_ERR_CUDA;
   return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
 }
 

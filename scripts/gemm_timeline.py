@@ -13,7 +13,7 @@ from fpga_ai_nic_b200.ops import kernels as K  # noqa: E402
 NAMES = ["entry", "dep_wait", "first_full", "mma_issued", "acc_done", "epi_done", "exit"]
 
 
-def run(kind, mb=1792, n=2048, k=2048, chain=8):
+def run(kind, bn=0, mb=1792, n=2048, k=2048, chain=8):
     torch.manual_seed(0)
     x = (torch.randn(mb, k, device="cuda") * 0.5).bfloat16()
     w = (torch.randn(n, k, device="cuda") * 0.02).bfloat16()
@@ -23,11 +23,11 @@ def run(kind, mb=1792, n=2048, k=2048, chain=8):
 
     def one(i):
         if kind == "NT":
-            K.gemm_fwd(x if i == 0 else y[(i + 1) & 1], w, out=y[i & 1])
+            K.gemm_fwd(x if i == 0 else y[(i + 1) & 1], w, out=y[i & 1], block_n=bn)
         elif kind == "NN":
-            K.gemm_bwd_data(dy if i == 0 else y[(i + 1) & 1], w, out=y[i & 1])
+            K.gemm_bwd_data(dy if i == 0 else y[(i + 1) & 1], w, out=y[i & 1], block_n=bn)
         else:
-            K.gemm_bwd_weight(dy, x, out=dw)
+            K.gemm_bwd_weight(dy, x, out=dw, block_n=bn)
 
     for _ in range(3):
         for i in range(chain):
@@ -42,7 +42,7 @@ def run(kind, mb=1792, n=2048, k=2048, chain=8):
     t = buf.cpu().double()
     live = t[:, :, 0] > 0
     t0 = t[0, :, 0][live[0]].min()
-    print(f"--- {kind} {mb}x{n}x{k}: chain of {chain}; us after the first entry of launch 0 (min / median / max over CTAs)")
+    print(f"--- {kind} block_n={bn} (negative = 2-CTA) {mb}x{n}x{k}: chain of {chain}; us after the first entry of launch 0 (min / median / max over CTAs)")
     for j in range(chain):
         m = live[j]
         if not m.any():
@@ -59,5 +59,7 @@ def run(kind, mb=1792, n=2048, k=2048, chain=8):
 
 
 if __name__ == "__main__":
-    for kind in (sys.argv[1:] or ["NT", "NN", "TN"]):
-        run(kind)
+    for spec in (sys.argv[1:] or ["NT", "NN", "TN"]):   # KIND[:block_n[:mb:n:k]]
+        f = spec.split(":")
+        dims = [int(v) for v in f[2:5]] if len(f) >= 5 else [1792, 2048, 2048]
+        run(f[0], int(f[1]) if len(f) > 1 else 0, *dims)
