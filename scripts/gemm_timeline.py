@@ -20,12 +20,15 @@ def run(kind, bn=0, mb=1792, n=2048, k=2048, chain=8):
     dy = (torch.randn(mb, n, device="cuda") * 0.1).bfloat16()
     y = [torch.empty(mb, n, dtype=torch.bfloat16, device="cuda") for _ in range(2)]
     dw = torch.empty(n, k, dtype=torch.float32, device="cuda")
+    cg = torch.empty(K.bfp_bytes(n * k), dtype=torch.uint8, device="cuda")
 
     def one(i):
         if kind == "NT":
             K.gemm_fwd(x if i == 0 else y[(i + 1) & 1], w, out=y[i & 1], block_n=bn)
         elif kind == "NN":
             K.gemm_bwd_data(dy if i == 0 else y[(i + 1) & 1], w, out=y[i & 1], block_n=bn)
+        elif kind == "TNC":   # weight gradient emitted as BFP frames (what the trainer does from 2 ranks on)
+            K.gemm_bwd_weight(dy, x, compressed_out=cg, block_n=bn)
         else:
             K.gemm_bwd_weight(dy, x, out=dw, block_n=bn)
 

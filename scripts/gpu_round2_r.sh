@@ -3,6 +3,7 @@
 set -x
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
+export AINIC_NO_BUILD=1
 timeout 120 python scripts/debug_flow_small.py > gpurun_out/r_flow_default.log 2>&1; tail -5 gpurun_out/r_flow_default.log
 timeout 300 python scripts/gemm_timeline.py NT NT:256 NT:-256 NT:-208 NN:-256 TN:-256 NT:0:1792:8192:8192 NT:-256:1792:8192:8192 > gpurun_out/r_timeline.log 2>&1; echo "timeline rc=$?"; grep -v "^launch [0-46-7]" gpurun_out/r_timeline.log
 timeout 300 python scripts/gemm_epi_bench.py --out gpurun_out/r_gemm_epi_tma.json > gpurun_out/r_gemm_epi_tma.log 2>&1; echo "rc=$?"; grep ours gpurun_out/r_gemm_epi_tma.log
