@@ -57,7 +57,7 @@ def _ref_mm(a, b):
     return a.float() @ b.float()
 
 
-GEMM_SHAPES = [(128, 256, 64), (256, 512, 256), (384, 1024, 1088), (1792, 2048, 2048)]
+GEMM_SHAPES = [(128, 256, 64), (256, 512, 256), (384, 1024, 1088), (1792, 2048, 2048), (200, 328, 72)]   # last: ragged in every dimension
 
 
 @pytest.mark.parametrize("mb,n,k", GEMM_SHAPES)
@@ -105,7 +105,8 @@ def test_gemm_bwd_weight(K, mb, n, k, block_n):
 
 
 @pytest.mark.parametrize("codec,mode", [("bfp", O.CLEAN), ("bfp", O.HW_EXACT), ("mxfp8", 0)])
-@pytest.mark.parametrize("mb,n,k,block_n", [(256, 512, 256, 0), (1792, 2048, 2048, 0), (384, 256, 512, 128), (384, 384, 1024, 192)])
+@pytest.mark.parametrize("mb,n,k,block_n", [(256, 512, 256, 0), (1792, 2048, 2048, 0), (384, 256, 512, 128), (384, 384, 1024, 192),
+                                                 (256, 320, 1024, 256), (128, 2048, 4096, 256)])   # partial row tile; more tiles than SMs (direct + TMA epilogues mixed)
 def test_gemm_bwd_weight_compressed_epilogue(K, codec, mode, mb, n, k, block_n):
     """The weight-gradient GEMM can emit the wire format directly: its bytes must equal the standalone
     codec applied to the fp32 gradient the same kernel writes (hw/bfp_adapter.sv behind the adder tree)."""
