@@ -85,9 +85,11 @@ def main():
         return float(t.item())
 
     g_nvls = None
-    if world > 1 and comm.enable_nvls(max_count * 4 + (4 << 20)):
+    if world > 1 and comm.enable_nvls(max_count * 6 + (8 << 20)):
         g_nvls = comm.nvls_empty(max_count)
         g_nvls.normal_(0, 1e-3)
+        g_nvls16 = comm.nvls_empty(max_count, torch.bfloat16)
+        g_nvls16.normal_(0, 1e-3)
     elif rank == 0:
         print("# NVLS unavailable:", getattr(comm, "nvls_error", ""))
 
@@ -132,6 +134,26 @@ def main():
             hbm_bytes = size * 3.5
             roof_ms = max(wire / (NVLINK_GBS * 1e6), hbm_bytes / (hbm * 1e6))
             rows.append({"impl": "nvls/f32", "bytes": size, "ms": ms, "wire_bytes": wire, "roofline_ms": roof_ms,
+                         "roofline_frac": roof_ms / ms})
+            # bf16 bucket.  "nvls/bf16" = the collective alone (the producer already wrote bf16, as a GEMM epilogue
+            # would); "cast+nvls/bf16" = fp32 gradient -> bf16 cast kernel -> collective, comparable with the fused
+            # codecs above, which also start from the fp32 gradient.
+            gb = g_nvls16[:count]
+            ms = timed(lambda: comm.allreduce_nvls(gb, wv, 0.1, sv), iters)
+            wire = size * 0.5
+            hbm_bytes = size * (0.5 * 2 + 2 + 0.5)      # bf16 bucket read + multicast write, fp32 weights r/w, bf16 shadow
+            roof_ms = max(wire / (NVLINK_GBS * 1e6), hbm_bytes / (hbm * 1e6))
+            rows.append({"impl": "nvls/bf16", "bytes": size, "ms": ms, "wire_bytes": wire, "roofline_ms": roof_ms,
+                         "roofline_frac": roof_ms / ms})
+
+            def cast_nvls():
+                K.cast_bf16(gv, out=gb)
+                comm.allreduce_nvls(gb, wv, 0.1, sv)
+
+            ms = timed(cast_nvls, iters)
+            hbm_bytes = size * (1 + 0.5 + 0.5 * 2 + 2 + 0.5)
+            roof_ms = max(wire / (NVLINK_GBS * 1e6), hbm_bytes / (hbm * 1e6))
+            rows.append({"impl": "cast+nvls/bf16", "bytes": size, "ms": ms, "wire_bytes": wire, "roofline_ms": roof_ms,
                          "roofline_frac": roof_ms / ms})
         size *= 4
     for r in rows:

@@ -368,6 +368,103 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_nvls_kernel(const Nvls
   }
 }
 
+// ---- bf16 gradients (two bytes per value on the wire and in HBM, no encode / decode work) --------------
+// The gradient bucket holds bf16 values (written by a cast kernel or a bf16 GEMM epilogue).  Unit of
+// work = 256 values = one 16-byte multimem operation per lane; lane l owns values 8 l .. 8 l + 7 of the
+// unit, so its weights are two adjacent float4 and its shadow one 16-byte store.
+__device__ __forceinline__ void apply_bf16x8(const RankCtx& c, size_t idx, uint4 g) {
+  if (!c.weight) return;
+  float4 w0 = *reinterpret_cast<const float4*>(c.weight + idx);
+  float4 w1 = *reinterpret_cast<const float4*>(c.weight + idx + 4);
+  const float nlr = -c.lr;
+  w0.x = fmaf(nlr, __uint_as_float(g.x << 16), w0.x);
+  w0.y = fmaf(nlr, __uint_as_float(g.x & 0xFFFF0000u), w0.y);
+  w0.z = fmaf(nlr, __uint_as_float(g.y << 16), w0.z);
+  w0.w = fmaf(nlr, __uint_as_float(g.y & 0xFFFF0000u), w0.w);
+  w1.x = fmaf(nlr, __uint_as_float(g.z << 16), w1.x);
+  w1.y = fmaf(nlr, __uint_as_float(g.z & 0xFFFF0000u), w1.y);
+  w1.z = fmaf(nlr, __uint_as_float(g.w << 16), w1.z);
+  w1.w = fmaf(nlr, __uint_as_float(g.w & 0xFFFF0000u), w1.w);
+  *reinterpret_cast<float4*>(c.weight + idx) = w0;
+  *reinterpret_cast<float4*>(c.weight + idx + 4) = w1;
+  if (c.wshadow) {
+    __nv_bfloat162 a = __floats2bfloat162_rn(w0.x, w0.y), b = __floats2bfloat162_rn(w0.z, w0.w);
+    __nv_bfloat162 d = __floats2bfloat162_rn(w1.x, w1.y), e = __floats2bfloat162_rn(w1.z, w1.w);
+    uint4 o;
+    o.x = *reinterpret_cast<uint32_t*>(&a);
+    o.y = *reinterpret_cast<uint32_t*>(&b);
+    o.z = *reinterpret_cast<uint32_t*>(&d);
+    o.w = *reinterpret_cast<uint32_t*>(&e);
+    *reinterpret_cast<uint4*>(c.wshadow + idx) = o;
+  }
+}
+
+// Start barrier -> owner: in-switch sum of its shard (multimem.ld_reduce, fp32 accumulation, bf16 result),
+// multicast of the sum into every rank's bucket, SGD on the shard -> barrier -> everyone applies the other
+// shards from its local bucket.  Every rank applies the same bf16 bits, so replicas stay identical.
+__global__ void __launch_bounds__(kCommThreads) allreduce_nvls_bf16_kernel(const NvlsCtx x) {
+  const RankCtx& c = x.base;
+  __shared__ WaitStats ws;
+  if (threadIdx.x == 0) begin_call(c, ws);
+  const unsigned long long t0 = ptx::globaltimer_ns();
+  __syncthreads();
+  const int cta = blockIdx.x, nctas = gridDim.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int N = c.nranks;
+  constexpr size_t kUnit = 256;                       // values per warp-wide 16-byte operation
+  constexpr int kBatch = 4;                           // units in flight per warp
+  const size_t units = c.count / kUnit;               // host enforces count % 512 == 0
+  const size_t shard = ((units + N - 1) / N + kBatch - 1) / kBatch * kBatch;
+  const __nv_bfloat16* gl = reinterpret_cast<const __nv_bfloat16*>(c.grad);
+  __nv_bfloat16* gmc = reinterpret_cast<__nv_bfloat16*>(x.grad_mc);
+  signal_all(c, 0, cta, ws.epoch);
+  wait_all(c, 0, cta, ws.epoch, ws);
+  fence_alias();
+  const size_t stride = (size_t)nctas * wpb * kBatch;
+  for (size_t j = ((size_t)cta + (size_t)warp * nctas) * kBatch; j < shard; j += stride) {
+    const size_t u0 = (size_t)c.rank * shard + j;
+    uint4 s[kBatch];
+#pragma unroll
+    for (int i = 0; i < kBatch; ++i)
+      if (u0 + i < units) s[i] = ptx::multimem_ld_reduce_bf16x8(gmc + (u0 + i) * kUnit + lane * 8);
+#pragma unroll
+    for (int i = 0; i < kBatch; ++i)
+      if (u0 + i < units) ptx::multimem_st_bf16x8(gmc + (u0 + i) * kUnit + lane * 8, s[i]);
+#pragma unroll
+    for (int i = 0; i < kBatch; ++i)
+      if (u0 + i < units) apply_bf16x8(c, (u0 + i) * kUnit + lane * 8, s[i]);
+  }
+  fence_alias();
+  signal_all(c, 1, cta, ws.epoch);
+  wait_all(c, 1, cta, ws.epoch, ws);
+  fence_alias();
+  for (int dp = 1; dp < N; ++dp) {
+    const int p = (c.rank + dp) % N;
+    for (size_t j = ((size_t)cta + (size_t)warp * nctas) * kBatch; j < shard; j += stride) {
+      const size_t u0 = (size_t)p * shard + j;
+      uint4 s[kBatch];
+#pragma unroll
+      for (int i = 0; i < kBatch; ++i)
+        if (u0 + i < units) s[i] = ptx::ld_stream_v4(gl + (u0 + i) * kUnit + lane * 8);
+#pragma unroll
+      for (int i = 0; i < kBatch; ++i)
+        if (u0 + i < units) apply_bf16x8(c, (u0 + i) * kUnit + lane * 8, s[i]);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned long long t1 = ptx::globaltimer_ns();
+    if (ws.timeouts) atomicAdd(c.counters + CTR_TIMEOUTS, (unsigned long long)ws.timeouts);
+    if (cta == 0) {
+      atomicAdd(c.counters + CTR_BUSY_NS, t1 - t0);
+      atomicAdd(c.counters + CTR_WAIT_NS, ws.wait_ns);
+      atomicAdd(c.counters + CTR_LAUNCHES, 1ull);
+      c.counters[CTR_LAST_NS] = t1 - t0;
+    }
+    end_call(c, ws, nctas);
+  }
+}
+
 }  // namespace comm
 }  // namespace ainic
 
@@ -388,6 +485,11 @@ extern "C" int ainic_allreduce_nvls(ainic_comm_t* c, ainic_nvls_t* h, const aini
   if (a->max_ctas > 0) ctas = (size_t)a->max_ctas;
   if (ctas < 1) ctas = 1;
   if (ctas > 148) ctas = 148;
-  allreduce_nvls_kernel<<<(unsigned)ctas, kCommThreadsOverlap, 0, (cudaStream_t)stream>>>(x);
+  if (a->codec == AINIC_CODEC_BF16) {   // the bucket holds bf16 values: half the wire and HBM bytes of the fp32 form
+    if (a->grad_out) { ainic_set_error_("nvls: grad_out is not offered with a bf16 bucket"); return AINIC_ERR_UNSUPPORTED; }
+    allreduce_nvls_bf16_kernel<<<(unsigned)ctas, kCommThreadsOverlap, 0, (cudaStream_t)stream>>>(x);
+  } else {
+    allreduce_nvls_kernel<<<(unsigned)ctas, kCommThreadsOverlap, 0, (cudaStream_t)stream>>>(x);
+  }
   return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
 }

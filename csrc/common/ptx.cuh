@@ -301,8 +301,20 @@ __device__ __forceinline__ void multimem_st_v4(void* mc_ptr, uint4 v) {
                "f"(__uint_as_float(v.w))
                : "memory");
 }
-__device__ __forceinline__ void multimem_red_add_u32(uint32_t* mc_ptr, uint32_t v) {
-  asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;\n" ::"l"(mc_ptr), "r"(v) : "memory");
+// 8 bf16 values (16 bytes): every GPU's copy is read and added inside the switch with fp32 accumulation,
+// the sum comes back rounded to bf16.
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc_ptr) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];\n"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(mc_ptr)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_bf16x8(void* mc_ptr, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};\n" ::"l"(mc_ptr), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
 }
 
 // Programmatic dependent launch (PDL): wait for the prerequisite grid's memory / let dependents start.

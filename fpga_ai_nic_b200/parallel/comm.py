@@ -147,9 +147,12 @@ class Communicator:
     def allreduce_nvls(self, grad: torch.Tensor, weight: torch.Tensor | None = None, lr: float = 0.0,
                        weight_bf16: torch.Tensor | None = None, grad_out: torch.Tensor | None = None, max_ctas: int = 0,
                        stream=None) -> None:
+        """In-switch all-reduce + SGD of a bucket that lives in the NVLS heap (``nvls_empty``).  ``grad`` is fp32, or
+        bf16 (half the wire and HBM bytes: the switch accumulates in fp32 and returns / multicasts bf16 sums)."""
+        codec = K.CODEC_BF16 if grad.dtype == torch.bfloat16 else K.CODEC_F32
         a = N.AllreduceArgs(grad.data_ptr(), weight.data_ptr() if weight is not None else None,
                             weight_bf16.data_ptr() if weight_bf16 is not None else None,
-                            grad_out.data_ptr() if grad_out is not None else None, grad.numel(), lr, K.CODEC_F32, 0,
+                            grad_out.data_ptr() if grad_out is not None else None, grad.numel(), lr, codec, 0,
                             K.ALGO_NVLS, max_ctas)
         N.check(self.lib.ainic_allreduce_nvls(self.handle, self.nvls, C.byref(a), N.stream_ptr(stream)), "allreduce_nvls")
         K._count()

@@ -161,6 +161,38 @@ if world > 1:
         say(check="nvls", ok=ok, available=True, max_err=err, identical=ident, timeouts=ctr["timeouts"], last_us=ctr["last_ns"] / 1e3)
         if not ok or ctr["timeouts"]:
             fails.append(("nvls",))
+        # bf16 bucket: the switch accumulates in fp32 and returns bf16; tolerance = one bf16 rounding of the sum
+        count = (1 << 20) + 512 * 3          # not a multiple of the 4-unit batch or of the shard size
+        gb = comm.nvls_empty(count, torch.bfloat16)
+        gen = torch.Generator().manual_seed(900 + rank)
+        g16 = (torch.randn(count, generator=gen) * 1e-2).bfloat16()
+        w0 = torch.randn(count, generator=torch.Generator().manual_seed(9))
+        ok = True
+        for rep in range(3):
+            gb.copy_(g16)
+            wv = w_heap[:count]
+            wv.copy_(w0)
+            all_g = gather(gb)
+            torch.cuda.synchronize()
+            dist.barrier()
+            comm.allreduce_nvls(gb, wv, 0.1, sh[:count])
+            torch.cuda.synchronize()
+            exact = all_g.double().sum(0)
+            sums = gather(gb)
+            ident = all(torch.equal(sums[r], sums[0]) for r in range(world))
+            rel = ((sums[0].double() - exact).abs() / exact.abs().clamp_min(1e-30)).max().item()
+            w_want = O.sgd(w0, sums[0].float().cpu(), 0.1)           # every rank applies the multicast bf16 sum
+            err = (wv.cpu() - w_want).abs().max().item()
+            allw = gather(wv)
+            ident &= all(torch.equal(allw[r], allw[0]) for r in range(world))
+            shd = sh[:count].cpu().float()
+            ok &= rel <= 2.0 ** -8 and err == 0.0 and ident and torch.equal(shd, wv.cpu().bfloat16().float())
+        ok = all_ok(ok)
+        ctr = comm.counters()
+        say(check="nvls_bf16", ok=ok, sum_rel_err=rel, weight_err_vs_applied_sum=err, identical=ident, timeouts=ctr["timeouts"],
+            last_us=ctr["last_ns"] / 1e3)
+        if not ok or ctr["timeouts"]:
+            fails.append(("nvls_bf16",))
 
 # ------------------------------------------------------------------ 2. NIC command interface, GPU backend
 nic = Nic("gpu", comm=comm, rank=rank, nranks=world)
