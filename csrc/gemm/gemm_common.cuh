@@ -370,6 +370,8 @@ __device__ __forceinline__ void epilogue_store(const EpiParams& ep, uint32_t tad
 // conflict-free for the row-per-lane writes) and one lane hands every finished box to the TMA unit,
 // which writes whole 128-byte lines and clips at the matrix edge.  No box is reused, so nothing
 // waits until the final wait_group.read before the CTA lets go of its shared memory.
+// The compressed (BFP / MXFP8) epilogues do not use this: their time is the quantiser's ALU work, which hides
+// the scattered 16-byte stores; a 3-D TMA-store version of them measured 0.7 us SLOWER (3.8 vs 3.1 us).
 // slab = this TMEM lane quarter's BLOCK_N / box-columns boxes (1024-byte aligned); row0 = first row.
 template <int BLOCK_N, int OUT>
 __device__ __forceinline__ void epilogue_store_tma(const EpiParams& ep, const CUtensorMap* tmap_c, uint32_t taddr, int row0,
@@ -449,76 +451,6 @@ __device__ __forceinline__ void epilogue_store_tma(const EpiParams& ep, const CU
   __syncwarp();
 }
 
-// Compressed (BFP / MXFP8) epilogue of a CTA's LAST tile through the idle operand ring and TMA stores.
-// Rows of the output are whole frames here (ldc % 512 == 0, 512 % BLOCK_N == 0), so the BLOCK_N mantissa
-// bytes a row contributes are contiguous inside ONE frame: the frame buffer is a 3-D tensor
-// {byte in frame, frame in row, row} and 128 bytes x 32 rows are one box.  Each lane quantises its row
-// 32 columns at a time (same bits as store_compressed32), parks the 32 bytes in the box in the
-// SWIZZLE_128B pattern, and one lane issues a store per finished box; only the exponent / scale bytes
-// (BLOCK_N / 16 or / 32 per row) leave with an ordinary store.  The direct epilogue's 16-byte stores
-// to 32 different frames per instruction disappear.  slab = BLOCK_N / 128 boxes of 4 KiB, 1024-aligned.
-template <int BLOCK_N>
-__device__ __forceinline__ void epilogue_store_frames_tma(const EpiParams& ep, const CUtensorMap* tmap_cg, uint32_t taddr, int row0,
-                                                          int n0, uint8_t* slab, int lane) {
-  static_assert(512 % BLOCK_N == 0 && BLOCK_N >= 128, "row spans must not straddle frames");
-  const bool bfp = ep.codec == AINIC_CODEC_BFP;
-  const size_t fbytes = bfp ? (size_t)kBfpFrameBytes : (size_t)kMxFrameBytes;
-  const uint32_t sw = (uint32_t)(lane & 7);
-  uint32_t r[32];
-  tmem_ld_32x32b_x32(taddr, r);
-  // NOT unrolled: the quantiser is ~300 instructions per 32 values per codec variant, and an unrolled epilogue
-  // (8 copies) no longer fits the instruction cache - measured 1 us slower than the direct stores it replaces
-  unsigned long long side = 0;       // BFP: 2 exponent bytes per 32 columns; MX: 1 scale byte; per 128-column box
-#pragma unroll 1
-  for (int c = 0; c < BLOCK_N / 32; ++c) {
-    const int b = c >> 2, q = c & 3;
-    uint8_t* box = slab + b * 4096;
-    uint4* srow = reinterpret_cast<uint4*>(box + lane * 128);
-    tmem_ld_wait();
-    float v[32];
-#pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * ep.alpha;
-    uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    if (bfp) {
-      const uint32_t sb = ep.bfp_mode == AINIC_BFP_HW_EXACT ? bfp_pack32<AINIC_BFP_HW_EXACT>(v, w) : bfp_pack32<AINIC_BFP_CLEAN>(v, w);
-      side |= (unsigned long long)sb << (16 * q);
-    } else {
-      uint32_t mag = 0;
-#pragma unroll
-      for (int j = 0; j < 32; ++j) mag = max(mag, __float_as_uint(v[j]) & 0x7FFFFFFFu);
-      const uint32_t sb = mx_scale_byte(mag >> 23);
-      const float inv = mx_inv_scale(sb);
-#pragma unroll
-      for (int j = 0; j < 32; ++j) w[j >> 2] |= f32_to_e4m3(v[j] * inv) << (8 * (j & 3));
-      side |= (unsigned long long)sb << (8 * q);
-    }
-    // the values are packed: their registers are free for the next chunk's TMEM read, which is then in
-    // flight during the shared-memory stores, the fence and the TMA issue
-    if (c + 1 < BLOCK_N / 32) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, r);
-    srow[(uint32_t)(q * 2) ^ sw] = make_uint4(w[0], w[1], w[2], w[3]);
-    srow[(uint32_t)(q * 2 + 1) ^ sw] = make_uint4(w[4], w[5], w[6], w[7]);
-    if (q == 3) {   // box complete
-      fence_proxy_async();
-      __syncwarp();
-      if (lane == 0 && row0 < ep.M) tma_store_3d(tmap_cg, box, (n0 & 511) + b * 128, n0 >> 9, row0);
-      // exponents / scales of this lane's own row for these 128 columns
-      if (row0 + lane < ep.M) {
-        const size_t flat = (size_t)(row0 + lane) * ep.ldc + n0;    // this lane's row inside the flat bucket
-        uint8_t* const fr = ep.cgrad + (flat >> 9) * fbytes;        // its frame (rows are whole frames)
-        const uint32_t off = (uint32_t)(flat & 511);
-        if (bfp) *reinterpret_cast<uint2*>(fr + kBfpExpOff + (off >> 4) + b * 8) = make_uint2((uint32_t)side, (uint32_t)(side >> 32));
-        else *reinterpret_cast<uint32_t*>(fr + kMxScaleOff + (off >> 5) + b * 4) = (uint32_t)side;
-      }
-      side = 0;
-    }
-  }
-  if (lane == 0) {
-    tma_store_commit();
-    tma_store_wait_read<0>();
-  }
-  __syncwarp();
-}
-
 // ------------------------------------------------------------------------------------------ host
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -550,34 +482,6 @@ inline int make_tmap(CUtensorMap* map, const void* base, uint64_t rows, uint64_t
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? AINIC_OK : AINIC_ERR_CUDA;
-}
-
-// Frame buffer of a [rows][ld] fp32-equivalent matrix whose rows are whole 512-value frames, as a 3-D byte
-// tensor {byte in frame (fbytes), frame in row (ld / 512), row}; box = 128 mantissa bytes x 1 x 32 rows.
-inline int make_tmap_frames(CUtensorMap* map, const void* base, uint64_t rows, uint64_t ld, uint64_t fbytes) {
-  EncodeTiledFn fn = get_encode_fn();
-  if (!fn) return AINIC_ERR_CUDA;
-  cuuint64_t gdim[3] = {fbytes, ld / 512, rows};
-  cuuint64_t gstride[2] = {fbytes, fbytes * (ld / 512)};
-  cuuint32_t box[3] = {128, 1, 32};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), gdim, gstride, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? AINIC_OK : AINIC_ERR_CUDA;
-}
-inline int cached_tmap_frames(CUtensorMap* out, const void* base, uint64_t rows, uint64_t ld, uint64_t fbytes) {
-  constexpr int kSlots = 64;
-  struct Slot { const void* base; uint64_t rows, ld, fbytes; CUtensorMap map; bool valid; };
-  static thread_local Slot slots[kSlots];
-  Slot& s = slots[((reinterpret_cast<uint64_t>(base) >> 8) ^ (reinterpret_cast<uint64_t>(base) >> 20) ^ rows ^ (ld << 3)) % kSlots];
-  if (!(s.valid && s.base == base && s.rows == rows && s.ld == ld && s.fbytes == fbytes)) {
-    const int rc = make_tmap_frames(&s.map, base, rows, ld, fbytes);
-    if (rc) { s.valid = false; return rc; }
-    s.base = base; s.rows = rows; s.ld = ld; s.fbytes = fbytes; s.valid = true;
-  }
-  *out = s.map;
-  return AINIC_OK;
 }
 
 // Encoding a tensor map costs a driver call (~1-2 us); a training step re-uses the same ~60 maps
@@ -636,8 +540,8 @@ inline int gemm_epi_sleep_ns() {
 // Last-tile epilogue through shared memory + TMA stores (epilogue_store_tma); AINIC_GEMM_TMA_STORE=0 keeps
 // the direct row-per-lane stores everywhere.
 inline bool tma_store_enabled() {
-  static const bool on = !(getenv("AINIC_GEMM_TMA_STORE") && atoi(getenv("AINIC_GEMM_TMA_STORE")) == 0);
-  return on;
+  const char* e = getenv("AINIC_GEMM_TMA_STORE");   // read per call (cheap): A/B runs switch it inside one process
+  return !(e && atoi(e) == 0);
 }
 
 // ainic_gemm_trace state: the next `left` launches write their per-CTA time stamps to consecutive [148][8]

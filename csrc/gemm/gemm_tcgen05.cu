@@ -189,13 +189,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         } else {
           epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
         }
-      } else if constexpr (OUT_F32 == OUT_COMPRESSED && 512 % BLOCK_N == 0 && BLOCK_N >= 128) {
-        if (ep.tma_out && epi_warps == 4 && tile + (int)gridDim.x >= num_tiles) {
-          constexpr int kSlab = (BLOCK_N / 128) * 4096;
-          epilogue_store_frames_tma<BLOCK_N>(ep, &tmap_c, taddr, m0 + quarter * 32, n0, smem + quarter * kSlab, lane);
-        } else {
-          epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
-        }
       } else {
         epilogue_store<BLOCK_N, OUT_F32>(ep, taddr, m0 + quarter * 32 + lane, n0, warp >= 6, epi_warps / 4);
       }
@@ -242,9 +235,7 @@ static int launch(const void* a, int lda, const void* b, int ldb, const EpiParam
   else rc = cached_tmap(&tb, b, ep.N, ep.K, ldb, BLOCK_K, BLOCK_N);
   if (rc) return rc;
   // output map of the TMA-store epilogue: 128-byte-wide, 32-row boxes (one per epilogue warp and column group)
-  if (ep.tma_out && ep.cgrad)
-    rc = cached_tmap_frames(&tc, ep.cgrad, ep.M, ep.ldc, ep.codec == AINIC_CODEC_BFP ? kBfpFrameBytes : kMxFrameBytes);
-  else if (ep.tma_out) rc = cached_tmap(&tc, ep.c, ep.M, ep.N, ep.ldc, OUT_F32 == OUT_FP32 ? 32 : 64, 32, OUT_F32 == OUT_FP32);
+  if (ep.tma_out) rc = cached_tmap(&tc, ep.c, ep.M, ep.N, ep.ldc, OUT_F32 == OUT_FP32 ? 32 : 64, 32, OUT_F32 == OUT_FP32);
   else tc = ta;
   if (rc) return rc;
   auto kern = gemm_kernel<BLOCK_N, A_MN, B_MN, OUT_F32>;
@@ -352,9 +343,6 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
   }
   ep.tma_out = tma_store_enabled() && c && !ep.cgrad && !ep.accumulate && !ep.mask_out && !ep.mask_in && !ep.done_flag &&
                ((uintptr_t)c & 15) == 0 && (layout != AINIC_GEMM_TN || (ldc % 4) == 0);
-  // compressed frames: whole-frame rows, whole tiles, local buffer (the scatter epilogue addresses peers per frame)
-  if (tma_store_enabled() && ep.cgrad && ep.push_n <= 1 && !ep.done_flag && !ep.stage_frames && (ldc % 512) == 0 && N == ldc)
-    ep.tma_out = 1;
   if (ep.cgrad) {  // compressed gradient output: backward-weight layout only, whole 32-value groups
     if (layout != AINIC_GEMM_TN || (N % 32) || (ldc % 32) || ((uintptr_t)ep.cgrad & 15) ||
         (ep.codec != AINIC_CODEC_BFP && ep.codec != AINIC_CODEC_MXFP8))
