@@ -162,7 +162,7 @@ if world > 1:
         if not ok or ctr["timeouts"]:
             fails.append(("nvls",))
         # bf16 bucket: the switch accumulates in fp32 and returns bf16; tolerance = one bf16 rounding of the sum
-        count = (1 << 20) + 512 * 3          # not a multiple of the 4-unit batch or of the shard size
+        count = (1 << 20) - 512 * 3          # not a multiple of the 4-unit batch or of the shard size
         gb = comm.nvls_empty(count, torch.bfloat16)
         gen = torch.Generator().manual_seed(900 + rank)
         g16 = (torch.randn(count, generator=gen) * 1e-2).bfloat16()
