@@ -525,19 +525,15 @@ inline int num_sms() {
   return n;
 }
 
-// Threads per CTA: 2 non-epilogue warps + 4 or 8 epilogue warps (two per TMEM lane quarter, each draining half
-// of the columns).  Plain outputs: 4 - their kernels use up to 88 registers and a third warp per SM sub-partition
-// would push an all-reduce CTA off the SM (3 x 32 x 88 + 2 x 32 x 144 > 16 K registers per sub-partition; that, not
-// the extra polling, is why 8 warps measured slower in the step: 0.815 vs 0.768 ms at 2 GPUs).  Compressed outputs:
-// 8 - the epilogue is the quantiser's ALU work on one warp per sub-partition (3.1 us), the kernel needs 72
-// registers (3 x 32 x 72 + 2 x 32 x 144 = 16128 fits), and the doorbell (flow) variant keeps 4 because the flow
-// kernel's 168 registers leave no room.  AINIC_GEMM_EPI_WARPS=4|8 forces one value everywhere.
-inline int gemm_threads(bool compressed = false, bool doorbell = false) {
+// Threads per CTA: 2 non-epilogue warps + 4 (default) or 8 (AINIC_GEMM_EPI_WARPS=8) epilogue warps (two per TMEM
+// lane quarter, each draining half of the columns).  8 warps do not pay: with the plain-output kernels (up to 88
+// registers) a third warp per SM sub-partition pushes an all-reduce CTA off the SM (3 x 32 x 88 + 2 x 32 x 144 >
+// 16 K registers per sub-partition: 0.815 vs 0.768 ms/step at 2 GPUs), and in the compressed-output kernel
+// (67 registers, fits) the epilogue takes 3.3 us with 8 warps against 3.1 us with 4 (profiles/README.md R2.7) -
+// it is not bound by per-warp work.
+inline int gemm_threads() {
   const char* e = getenv("AINIC_GEMM_EPI_WARPS");
-  const int forced = e ? atoi(e) : 0;
-  if (forced == 8) return kThreads;
-  if (forced == 4) return 192;
-  return (compressed && !doorbell) ? kThreads : 192;
+  return (e && atoi(e) == 8) ? kThreads : 192;
 }
 inline int gemm_epi_sleep_ns() {
   static const int v = getenv("AINIC_GEMM_EPI_SLEEP") ? atoi(getenv("AINIC_GEMM_EPI_SLEEP")) : 0;

@@ -41,8 +41,8 @@ __host__ __device__ constexpr uint32_t tmem_cols(int block_n) {
 // are allocated per SM sub-partition (16 K each): the all-reduce CTA's 8 warps put two on each sub-partition
 // (2 x 32 x 144 registers for the overlap kernels, x 168 for the flow kernel), this kernel's 6 warps up to
 // two more, which leaves 112 / 88 registers per thread.  With 96 the flow kernel's doorbells were never
-// rung: the GEMM CTAs could not become resident beside it.  The compressed-output kernels run 8 epilogue
-// warps (gemm_threads), i.e. up to three warps per sub-partition: 72.
+// rung: the GEMM CTAs could not become resident beside it.  The compressed-output kernels are held at 72 so that
+// they still fit with eight epilogue warps (AINIC_GEMM_EPI_WARPS=8: three warps per sub-partition).
 template <int BLOCK_N, bool A_MN, bool B_MN, int OUT_F32>
 __global__ void __maxnreg__(OUT_F32 == OUT_COMPRESSED ? 72 : 88)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
@@ -253,7 +253,7 @@ static int launch(const void* a, int lda, const void* b, int ldb, const EpiParam
   if (tiles < grid) grid = tiles;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(gemm_threads(OUT_F32 == OUT_COMPRESSED, ep.done_flag != nullptr));
+  cfg.blockDim = dim3(gemm_threads());
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
