@@ -11,7 +11,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "fpga_ai_nic_b200", "_lib", "libainic_cuda.so")
 KEYS = ["UTCHMMA", "UTCQMMA", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTCBAR", "UTCATOMSWS", "UCGABAR", "SYNCS", "LDGMC",
-        "STG.E.MC", "REDG", "HMMA", "LDG.E", "STG.E", "ERRBAR", "MEMBAR", "FFMA", "SHFL", "STL", "LDL", "ACQBULK", "NANOSLEEP"]
+        "REDG", "HMMA", "LDG.E", "STG.E", "ERRBAR", "MEMBAR", "FFMA", "SHFL", "STL", "LDL", "ACQBULK", "NANOSLEEP"]
 
 
 def main():
