@@ -257,6 +257,7 @@ def run_ours(args, rank, local, world):
                "ms_per_step": ms_e2e / args.steps,
                "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": 4,
                "h2d_copy_alone_ms": h2d_ms, "h2d_copy_alone_gbps": in_bytes / h2d_ms / 1e6,
+               "numa_bind": getattr(tr.comm, "numa", None),
                "note": "fp32 inputs from pinned host memory every step (prefetched one step ahead on a copy stream), "
                        "cast to bf16 on device; every step's loss is copied to pinned host memory and read by the "
                        "host one step later (the last one before the closing event)"}
@@ -323,6 +324,9 @@ def run_ddp(args, rank, local, world, mode="naive"):
     import torch.nn as nn
     import torch.nn.functional as F
     dev = torch.device("cuda", local)
+    if world > 1:   # same host-side placement as the product arm (Communicator binds its rank the same way)
+        from fpga_ai_nic_b200.utils.numa import bind_to_gpu
+        bind_to_gpu(local)
     torch.manual_seed(1)
     hardened = mode in ("hardened", "hardened-eager")
     try_graph = mode == "hardened"
