@@ -134,6 +134,7 @@ class MLPTrainer:
         self.act_dtype = torch.float32 if cfg.dtype == "f32" else torch.bfloat16
         self.loss_dev = torch.zeros(1, dtype=torch.float32, device=self.device)
         self._views: dict = {}
+        self._wver = 0        # bumped whenever the weights may have changed (forward_mx re-quantises its copies)
         self.init_weights()
 
     # -- buffers ------------------------------------------------------------------------------
@@ -202,6 +203,7 @@ class MLPTrainer:
         return xs, ys
 
     def sync_shadows(self) -> None:
+        self._wver += 1
         N.check(self.lib.ainic_mlp_sync_shadows(self.handle, N.stream_ptr()), "mlp_sync_shadows")
         torch.cuda.current_stream().synchronize()
 
@@ -211,6 +213,37 @@ class MLPTrainer:
         N.check(self.lib.ainic_mlp_forward(self.handle, x.data_ptr(), N.stream_ptr()), "mlp_forward")
         return self.buffer("act", self.cfg.nlayers)
 
+    def forward_mx(self, x: torch.Tensor) -> torch.Tensor:
+        """Inference forward pass on the block-scaled fp8 tensor-core kind (tcgen05.mma.kind::mxf8f6f4.block_scale):
+        weights are quantised once per weight version (e4m3 + one ue8m0 scale per 32 inputs, from the bf16 shadows),
+        activations by one quantiser launch per layer, accumulation is fp32, layer outputs are bf16.  The GEMM is
+        1.3-1.6 x the bf16 one (profiles/README.md R2.4); training keeps bf16 operands.
+        Returns the logits (bf16, a buffer reused by the next call).  Layer widths must be multiples of 128."""
+        cfg = self.cfg
+        assert cfg.dtype == "bf16" and x.dtype == torch.bfloat16 and x.is_cuda and x.is_contiguous()
+        assert all(s % 128 == 0 for s in cfg.sizes), "MX forward: layer widths must be multiples of 128"
+        st = self.__dict__.setdefault("_mx", {"version": None, "w": [], "act": {}, "out": {}})
+        version = self._wver
+        if st["version"] != version:          # (re)quantise the weights: training steps / loads change them
+            self.wait()
+            prev = st["w"] or [None] * cfg.nlayers
+            st["w"] = [K.mx_quantize_rows(self.buffer("shadow", l), out=prev[l]) for l in range(cfg.nlayers)]
+            st["version"] = version
+        h = x
+        for l in range(cfg.nlayers):
+            rows = h.shape[0]
+            key = (l, rows)
+            aq = st["act"][key] = K.mx_quantize_rows(h, out=st["act"].get(key))
+            if key not in st["out"]:
+                st["out"][key] = torch.empty(rows, cfg.sizes[l + 1], dtype=torch.bfloat16, device=h.device)
+            wq, wsf = st["w"][l]
+            h = K.gemm_mxfp8(K.GEMM_NT, aq[0], aq[1], wq, wsf, out=st["out"][key])
+            if cfg.fuse in (1, 3):
+                h.add_(self.buffer("bias", l).to(h.dtype))
+            if cfg.fuse >= 2:
+                h.relu_()
+        return h
+
     def step(self, x: torch.Tensor, labels: torch.Tensor, want_loss: bool = True,
              loss_out: torch.Tensor | None = None) -> torch.Tensor | None:
         """One training iteration (enqueue only).  Returns the device scalar holding this rank's
@@ -219,6 +252,7 @@ class MLPTrainer:
         assert x.dtype == self.act_dtype and x.is_cuda and x.is_contiguous()
         assert labels.dtype == torch.int32 and labels.is_cuda
         dst = loss_out if loss_out is not None else self.loss_dev
+        self._wver += 1
         N.check(self.lib.ainic_mlp_step(self.handle, x.data_ptr(), labels.data_ptr(),
                                         dst.data_ptr() if want_loss else None, N.stream_ptr()), "mlp_step")
         return dst if want_loss else None

@@ -301,13 +301,18 @@ def mx_sf_bytes(rows: int, k: int) -> int:
     return N.cuda().ainic_mx_sf_bytes(rows, k)
 
 
-def mx_quantize_rows(x: torch.Tensor):
+def mx_quantize_rows(x: torch.Tensor, out: tuple | None = None):
     """x [rows, K] (fp32 / bf16, K contiguous) -> (q uint8 [rows, K] e4m3, scale atoms uint8): one ue8m0 scale per 32
-    consecutive values of a row, stored in the tcgen05 scale-factor atom layout (gemm_kinds.cu)."""
+    consecutive values of a row, stored in the tcgen05 scale-factor atom layout (gemm_kinds.cu).  ``out`` = a
+    (q, scale atoms) pair from an earlier call with the same shape, to reuse its buffers."""
     assert x.is_cuda and x.dim() == 2 and x.stride(1) == 1 and x.dtype in (torch.float32, torch.bfloat16)
     rows, k = x.shape
-    q = torch.empty(rows, k, dtype=torch.uint8, device=x.device)
-    sf = torch.empty(mx_sf_bytes(rows, k), dtype=torch.uint8, device=x.device)
+    if out is not None:
+        q, sf = out
+        assert q.shape == (rows, k) and q.dtype == torch.uint8 and sf.numel() == mx_sf_bytes(rows, k)
+    else:
+        q = torch.empty(rows, k, dtype=torch.uint8, device=x.device)
+        sf = torch.empty(mx_sf_bytes(rows, k), dtype=torch.uint8, device=x.device)
     N.check(N.cuda().ainic_mx_quantize_rows(x.data_ptr(), int(x.dtype == torch.bfloat16), rows, k, x.stride(0), q.data_ptr(),
                                             sf.data_ptr(), N.stream_ptr()), "mx_quantize_rows")
     _count(2)

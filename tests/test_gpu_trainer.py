@@ -263,3 +263,33 @@ def test_f32_mode_matches_fp32_oracle():
         assert ((tr.buffer("weight", l).cpu() - W[l]).norm() / upd).item() < 5e-3
     assert tr.buffer("act", 1).dtype == torch.float32
     tr.close()
+
+
+def test_forward_mx_tracks_the_bf16_forward_and_the_weights():
+    """Inference on the block-scaled fp8 tensor-core kind: same logits as the bf16 forward up to e4m3 rounding
+    (one scale per 32 inputs), and the quantised weight copies follow the weights through a training step."""
+    from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer
+    from fpga_ai_nic_b200.ops import kernels as K
+    cfg = MLPConfig(sizes=[256, 384, 256, 128], mb=256, fuse=0, lr=0.5, loss_weight=1.0)
+    tr = MLPTrainer(cfg)
+    g = torch.Generator().manual_seed(5)
+    x = K.cast_bf16((torch.rand(cfg.mb, cfg.sizes[0], generator=g) - 0.5).cuda())
+    y = torch.randint(0, cfg.sizes[-1], (cfg.mb,), generator=g, dtype=torch.int32).cuda()
+
+    def rel(a, b):
+        return ((a.float() - b.float()).norm() / b.float().norm()).item()
+
+    ref0 = tr.forward(x).clone()
+    mx0 = tr.forward_mx(x).clone()
+    torch.cuda.synchronize()
+    assert rel(mx0, ref0) < 0.08
+    assert torch.equal(tr.forward_mx(x), mx0)            # deterministic, buffers reused
+    for _ in range(3):
+        tr.step(x, y)
+    tr.wait()
+    ref1 = tr.forward(x).clone()
+    mx1 = tr.forward_mx(x).clone()
+    torch.cuda.synchronize()
+    assert rel(ref1, ref0) > 0.01                        # the steps did move the weights
+    assert rel(mx1, ref1) < 0.08 and rel(mx1, ref1) < rel(mx0, ref1)
+    tr.close()
