@@ -289,28 +289,48 @@ __host__ __device__ inline size_t sf_offset(int r, int kblock, int K) {
 __device__ __forceinline__ float load_as_f32(const void* p, size_t i, bool bf16) {
   return bf16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i]) : reinterpret_cast<const float*>(p)[i];
 }
-// Blocks of 32 consecutive values along the contiguous dimension (K-major operands): one thread per block.
+// Blocks of 32 consecutive values along the contiguous dimension (K-major operands).  Four adjacent lanes share
+// a block, eight values each: a warp reads 256 consecutive values per load instruction (16 bytes per lane for
+// bf16, 2 x 16 for fp32) and writes 256 consecutive e4m3 bytes; the block maximum takes two xor-shuffles.
+// (One thread per block - 32 scalar loads 64 bytes apart between lanes - ran at 0.7-1.1 TB/s.)
 __global__ void mx_quantize_rows_kernel(const void* x, bool bf16, int rows, int K, int ld, uint8_t* q, uint8_t* sf) {
   const int kblocks = K >> 5;
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= (size_t)rows * kblocks) return;
-  const int r = (int)(t / kblocks), kb = (int)(t % kblocks);
-  float v[32];
+  const size_t blk = t >> 2;
+  const int part = (int)(t & 3);
+  const bool live = blk < (size_t)rows * kblocks;      // whole groups of four are live or dead together
+  const int r = live ? (int)(blk / kblocks) : 0, kb = live ? (int)(blk % kblocks) : 0;
+  const size_t src = (size_t)r * ld + kb * 32 + part * 8;
+  float v[8];
+  if (bf16) {
+    const uint4 p = live ? *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(x) + src) : make_uint4(0, 0, 0, 0);
+    const uint32_t w[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      v[2 * j] = __uint_as_float(w[j] << 16);
+      v[2 * j + 1] = __uint_as_float(w[j] & 0xFFFF0000u);
+    }
+  } else {
+    const float4 a = live ? *reinterpret_cast<const float4*>(static_cast<const float*>(x) + src) : make_float4(0, 0, 0, 0);
+    const float4 c = live ? *reinterpret_cast<const float4*>(static_cast<const float*>(x) + src + 4) : make_float4(0, 0, 0, 0);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
+  }
   uint32_t E = 0;
 #pragma unroll
-  for (int j = 0; j < 32; ++j) {
-    v[j] = load_as_f32(x, (size_t)r * ld + kb * 32 + j, bf16);
-    E = max(E, bfp_exp_field(__float_as_uint(v[j])));
-  }
+  for (int j = 0; j < 8; ++j) E = max(E, bfp_exp_field(__float_as_uint(v[j])));
+  E = max(E, __shfl_xor_sync(0xFFFFFFFFu, E, 1));
+  E = max(E, __shfl_xor_sync(0xFFFFFFFFu, E, 2));
+  if (!live) return;
   const uint32_t sb = mx_scale_byte(E);
   const float inv = mx_inv_scale(sb);
-  uint32_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  uint32_t w0 = 0, w1 = 0;
 #pragma unroll
-  for (int j = 0; j < 32; ++j) w[j >> 2] |= f32_to_e4m3(v[j] * inv) << (8 * (j & 3));
-  uint4* dst = reinterpret_cast<uint4*>(q + (size_t)r * K + kb * 32);
-  dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
-  dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
-  sf[sf_offset(r, kb, K)] = (uint8_t)sb;
+  for (int j = 0; j < 4; ++j) {
+    w0 |= f32_to_e4m3(v[j] * inv) << (8 * j);
+    w1 |= f32_to_e4m3(v[4 + j] * inv) << (8 * j);
+  }
+  *reinterpret_cast<uint2*>(q + (size_t)r * K + kb * 32 + part * 8) = make_uint2(w0, w1);
+  if (part == 0) sf[sf_offset(r, kb, K)] = (uint8_t)sb;
 }
 // Blocks of 32 consecutive ROWS of one column (MN-major operands: x is [K][cols], K is the slow dimension):
 // one thread per (column, row block); adjacent threads take adjacent columns, so every row access is coalesced.
@@ -466,9 +486,10 @@ extern "C" size_t ainic_mx_sf_bytes(size_t rows, size_t K) { return ((rows + 127
 // x: [rows][ld] (K contiguous) fp32 or bf16 -> q: [rows][K] e4m3 + scale atoms (one ue8m0 per 32 values along K)
 extern "C" int ainic_mx_quantize_rows(const void* x, int x_is_bf16, int rows, int K, int ld, void* q, void* sf, void* stream) {
   if (!x || !q || !sf || rows <= 0 || K <= 0 || (K % 128) || ld < K || ((uintptr_t)q & 15)) return AINIC_ERR_ARG;
+  if (((uintptr_t)x & 15) || (ld % (x_is_bf16 ? 8 : 4))) return AINIC_ERR_ARG;   // 16-byte vector loads
   cudaStream_t s = (cudaStream_t)stream;
   if (cudaMemsetAsync(sf, 0, ainic_mx_sf_bytes(rows, K), s) != cudaSuccess) return AINIC_ERR_CUDA;
-  const size_t n = (size_t)rows * (K / 32);
+  const size_t n = (size_t)rows * (K / 32) * 4;   // four lanes per 32-value block
   mx_quantize_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, x_is_bf16 != 0, rows, K, ld, static_cast<uint8_t*>(q),
                                                                        static_cast<uint8_t*>(sf));
   return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
