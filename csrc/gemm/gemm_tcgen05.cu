@@ -364,7 +364,7 @@ extern "C" int ainic_gemm_bf16(int layout, const void* a, int lda, const void* b
       const double e = wave_eff(M, N, 128, bn, sms) * 0.80;   // 1-CTA main loop is smem-bandwidth bound
       if (e > best * 1.02) { best = e; block_n = bn; }
     }
-    if (allow_2cta && M >= 256 && sms >= 2 && !ep.done_flag) {
+    if (allow_2cta && M >= 256 && sms >= 2 && !ep.done_flag && !ep.cgrad) {   // no doorbell / compressed epilogue there
       for (int i = 0; i < 2; ++i) {
         const int bn = kk ? cand2_kk[i] : cand2_mn[i];
         const double e = wave_eff(M, N, 256, bn, sms / 2);
