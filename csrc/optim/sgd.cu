@@ -6,7 +6,6 @@
 #include <cuda_runtime.h>
 
 #include "../../include/ainic.h"
-#include "../common/ptx.cuh"
 
 namespace ainic {
 
@@ -51,35 +50,6 @@ __global__ void __launch_bounds__(256) cast_kernel(const float* __restrict__ x, 
   if (t < count) y[t] = __float2bfloat16_rn(x[t]);
 }
 
-// Host -> device input upload as a kernel: a few CTAs read fp32 batches straight out of PINNED HOST memory
-// (unified addressing: the pinned pointer is valid on the device) with four 16-byte loads in flight per thread
-// and write bf16 to device memory.  Replaces cudaMemcpyAsync into a staging buffer + a cast pass: the bytes
-// cross PCIe once, no fp32 copy ever lands in HBM, and no copy-engine transfer runs beside the training step's
-// graph (measured: the DMA + cast cost the concurrent step ~4 %).  256 threads x 64 B x `ctas` must cover the
-// PCIe bandwidth-delay product (~55 GB/s x ~1.5 us = 80 KB): 8 CTAs keep 128 KB in flight.
-__global__ void __launch_bounds__(256) upload_cast_kernel(const float* __restrict__ host, __nv_bfloat16* __restrict__ y, size_t count) {
-  const size_t n16 = count >> 4;                       // 16 values = 64 host bytes per thread and iteration
-  const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) {
-    uint4 v[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) v[j] = ptx::ld_stream_v4(host + i * 16 + j * 4);
-    uint32_t o[8];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      __nv_bfloat162 a = __floats2bfloat162_rn(__uint_as_float(v[j].x), __uint_as_float(v[j].y));
-      __nv_bfloat162 b = __floats2bfloat162_rn(__uint_as_float(v[j].z), __uint_as_float(v[j].w));
-      o[2 * j] = *reinterpret_cast<uint32_t*>(&a);
-      o[2 * j + 1] = *reinterpret_cast<uint32_t*>(&b);
-    }
-    uint4* dst = reinterpret_cast<uint4*>(y + i * 16);
-    dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
-    dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
-  }
-  const size_t t = (n16 << 4) + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < count) y[t] = __float2bfloat16_rn(host[t]);
-}
-
 static int ew_grid(size_t count) {
   size_t b = (count / 4 + 255) / 256;
   const size_t cap = 148 * 8;
@@ -101,18 +71,5 @@ extern "C" int ainic_sgd(float* w, const float* g, void* w_bf16, size_t count, f
 extern "C" int ainic_cast_f32_bf16(const float* x, void* y, size_t count, void* stream) {
   if (!x || !y || count == 0 || ((uintptr_t)x & 15) || ((uintptr_t)y & 7)) return AINIC_ERR_ARG;
   cast_kernel<<<ew_grid(count), 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)y, count);
-  return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
-}
-
-extern "C" int ainic_upload_cast_bf16(const float* host_pinned, void* y, size_t count, int ctas, void* stream) {
-  if (!host_pinned || !y || count == 0 || ((uintptr_t)host_pinned & 15) || ((uintptr_t)y & 15)) return AINIC_ERR_ARG;
-  cudaPointerAttributes at{};
-  if (cudaPointerGetAttributes(&at, host_pinned) != cudaSuccess || at.type != cudaMemoryTypeHost) {
-    cudaGetLastError();
-    return AINIC_ERR_ARG;   // pageable memory is not addressable from the device
-  }
-  if (ctas <= 0) ctas = 8;
-  if (ctas > 148) ctas = 148;
-  upload_cast_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(static_cast<const float*>(at.devicePointer), (__nv_bfloat16*)y, count);
   return cudaGetLastError() == cudaSuccess ? AINIC_OK : AINIC_ERR_CUDA;
 }

@@ -148,7 +148,6 @@ def cuda() -> C.CDLL:
     lib.ainic_mx_decompress.argtypes = [vp, sz, vp, vp]
     lib.ainic_sgd.argtypes = [vp, vp, vp, sz, C.c_float, vp]
     lib.ainic_cast_f32_bf16.argtypes = [vp, vp, sz, vp]
-    lib.ainic_upload_cast_bf16.argtypes = [vp, vp, sz, C.c_int, vp]
     lib.ainic_gemm_bf16.argtypes = [C.c_int, vp, C.c_int, vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.POINTER(GemmEpilogue), C.c_int, C.c_int, vp]
     lib.ainic_gemm_trace.argtypes = [vp, C.c_int]

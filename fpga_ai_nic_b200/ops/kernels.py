@@ -103,18 +103,6 @@ def cast_bf16(x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     return out
 
 
-def upload_bf16(host_x: torch.Tensor, out: torch.Tensor, ctas: int = 0) -> torch.Tensor:
-    """Pinned host fp32 batch -> device bf16 in one kernel that reads the host memory over PCIe itself
-    (ainic_upload_cast_bf16): no staging copy, no cast pass, no copy-engine transfer beside the running step."""
-    assert host_x.dtype == torch.float32 and host_x.is_pinned() and host_x.is_contiguous()
-    _chk(out, torch.bfloat16)
-    assert out.numel() == host_x.numel()
-    N.check(N.cuda().ainic_upload_cast_bf16(host_x.data_ptr(), out.data_ptr(), host_x.numel(), int(ctas), N.stream_ptr()),
-            "upload_cast_bf16")
-    _count()
-    return out
-
-
 # ---------------------------------------------------------------- GEMMs
 def _gemm(layout, a, b, c, M, Nn, K, epi: N.GemmEpilogue | None, block_n=0, max_ctas=0, stream=None):
     lib = N.cuda()

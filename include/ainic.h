@@ -57,10 +57,6 @@ int ainic_mx_decompress(const uint8_t* in, size_t count, float* out, void* strea
  * w = fmaf(-lr, g, w); optional bf16 shadow of the new weights for the tensor-core GEMMs. */
 int ainic_sgd(float* w, const float* g, void* w_bf16 /*nullable*/, size_t count, float lr, void* stream);
 int ainic_cast_f32_bf16(const float* x, void* y_bf16, size_t count, void* stream);
-/* Input upload as a kernel: `ctas` CTAs (0 = 8) read an fp32 batch directly from PINNED host memory over PCIe and
- * write it as bf16 to device memory - one pass instead of cudaMemcpyAsync + cast, and no copy-engine transfer
- * beside the training step.  host_pinned: cudaHostAlloc / cudaHostRegister memory, 16-byte aligned. */
-int ainic_upload_cast_bf16(const float* host_pinned, void* y_bf16, size_t count, int ctas, void* stream);
 
 /* ---------------------------------------------------------------- MLP kernels (K1-K5) */
 #define AINIC_GEMM_NT 0 /* C[M,N] = A[M,K] . B[N,K]^T  bf16 out  (forward)        */

@@ -201,16 +201,3 @@ def test_bias_grad(K):
     ref = dy.float().sum(0)
     torch.cuda.synchronize()
     assert (got - ref).abs().max().item() <= 1e-3 * ref.abs().max().item() + 1e-4
-
-
-@pytest.mark.parametrize("count", [16, 1000, 1792 * 2048 + 5])
-def test_upload_cast_reads_pinned_host_memory(K, count):
-    """ainic_upload_cast_bf16: the kernel reads the pinned host batch itself; same bits as copy + cast; pageable memory is refused."""
-    g = torch.Generator().manual_seed(count)
-    hx = (torch.rand(count, generator=g) - 0.5).pin_memory()
-    out = torch.zeros(count, dtype=torch.bfloat16, device="cuda")
-    K.upload_bf16(hx, out=out)
-    torch.cuda.synchronize()
-    assert torch.equal(out.cpu(), hx.bfloat16())
-    with pytest.raises(AssertionError):
-        K.upload_bf16(torch.rand(count), out=out)
