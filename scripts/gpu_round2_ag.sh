@@ -22,4 +22,4 @@ for c in ('deep','wide'):
         print(c, 'ours', d.get('ms_per_step'), 'e2e', d['e2e'].get('ms_per_step'), 'vs', d.get('vs_baseline'), {k:(v.get('ms_per_step'), v.get('cuda_graph')) for k,v in b.items() if isinstance(v,dict)}, d.get('correctness'))
     except Exception as e: print(c, 'ERR', e)
 PY
-tail -3 gpurun_out/ag_*_n$N.err | cut -c1-300
+for f in gpurun_out/ag_*_n$N.err; do tail -n 3 $f | cut -c1-300; done
