@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"],
                     help="bf16: bf16 activations / weight shadows (headline); f32: the reference's all-fp32 data flow on tf32 tensor cores")
     ap.add_argument("--bucket-mb", type=float, default=None,
-                    help="fp32 MiB of gradients per fused all-reduce (0 = per layer; default: 80 from 2 ranks)")
+                    help="fp32 MiB of gradients per fused all-reduce (0 = per layer; default: 48 at 2 ranks, 80 from 3)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-baseline", action="store_true",
                     help="--impl ours: skip the PyTorch DDP arms that are otherwise measured in the same invocation")

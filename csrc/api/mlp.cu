@@ -207,7 +207,10 @@ extern "C" int ainic_mlp_create2(ainic_mlp_t** out, ainic_comm_t* comm, int nlay
     // exchanges plus the launch skew between ranks whatever its size; measured on the reference MLP
     // (ms/step, per-layer -> 80 MiB): 0.767 -> 0.700 at 2 ranks, 0.959 -> 0.784 at 8 ranks.
     const int n = ainic_comm_size(comm);
-    m->bucket_bytes = n >= 2 ? (size_t)80 << 20 : 0;
+    // 2 ranks (one-shot kernel, one flag exchange per call) do better with 48 MiB - three layers of the reference
+    // model per call - than with 80 (0.567 vs 0.578 ms/step); at 4 ranks 48 / 64 / 80 MiB measure 0.624 / 0.609 /
+    // 0.596 and at 8 ranks every schedule with more than two calls was slower (profiles/README.md R2.1, R2.9).
+    m->bucket_bytes = n == 2 ? (size_t)48 << 20 : n > 2 ? (size_t)80 << 20 : 0;
     if (const char* e = getenv("AINIC_BUCKET_MB")) m->bucket_bytes = (size_t)(atof(e) * 1048576.0);
     if (const char* e = getenv("AINIC_BUCKET_LAYERS")) {   // e.g. "4,3,2,1": big buckets first, a small exposed tail
       for (const char* p = e; *p;) {

@@ -59,7 +59,7 @@ class MLPConfig:
             return float(self.bucket_mb)
         if os.environ.get("AINIC_BUCKET_MB"):
             return float(os.environ["AINIC_BUCKET_MB"])
-        return 80.0 if world >= 2 else 0.0
+        return 48.0 if world == 2 else 80.0 if world > 2 else 0.0      # same rule as csrc/api/mlp.cu
 
     def bucket_plan(self, world: int = 1) -> list:
         """(lowest layer, highest layer) of every fused all-reduce call of one step, in issue order - the
