@@ -91,10 +91,6 @@ template <int N>
 __device__ __forceinline__ void tma_store_wait_read() {
   asm volatile("cp.async.bulk.wait_group.read %0;\n" ::"n"(N) : "memory");
 }
-template <int N>
-__device__ __forceinline__ void tma_store_wait() {
-  asm volatile("cp.async.bulk.wait_group %0;\n" ::"n"(N) : "memory");
-}
 
 // ------------------------------------------------------------------ tcgen05 / TMEM
 template <uint32_t kCols>
