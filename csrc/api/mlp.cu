@@ -277,9 +277,18 @@ extern "C" int ainic_mlp_create2(ainic_mlp_t** out, ainic_comm_t* comm, int nlay
   return AINIC_OK;
 }
 
-extern "C" int ainic_mlp_destroy(ainic_mlp_t* m) {
+// free_heap: give the weight / gradient arenas back to the communicator's symmetric heap.  Only safe when no
+// peer can still be reading them, i.e. with one rank or behind a barrier (MLPTrainer.close does that); every rank
+// must then make the same choice so that the heaps stay symmetric.
+extern "C" int ainic_mlp_destroy_ex(ainic_mlp_t* m, int free_heap) {
   if (!m) return AINIC_ERR_ARG;
   cudaDeviceSynchronize();
+  if (free_heap) {
+    for (int i = 1; i >= 0; --i)
+      if (m->cg_arena[i]) ainic_comm_free(m->comm, m->cg_arena[i]);
+    if (m->g_arena) ainic_comm_free(m->comm, m->g_arena);
+    if (m->w_arena) ainic_comm_free(m->comm, m->w_arena);
+  }
   for (auto& L : m->layers) {
     cudaFree(L.bias); cudaFree(L.dbias); cudaFree(L.mask);
     cudaEventDestroy(L.dy_ready); cudaEventDestroy(L.dw_ready); cudaEventDestroy(L.updated); cudaEventDestroy(L.dx_done);
@@ -299,6 +308,9 @@ extern "C" int ainic_mlp_destroy(ainic_mlp_t* m) {
   cudaStreamDestroy(m->comm_stream);
   delete m;
   return AINIC_OK;
+}
+extern "C" int ainic_mlp_destroy(ainic_mlp_t* m) {
+  return m ? ainic_mlp_destroy_ex(m, ainic_comm_size(m->comm) == 1) : AINIC_ERR_ARG;
 }
 
 // Raw buffer access for initialisation, checkpointing and tests.

@@ -10,8 +10,10 @@
 
 #include <mutex>
 #include <string>
+#include <vector>
 
 #include "allreduce.cuh"
+#include "heap_alloc.h"
 #include "flow.cuh"
 
 using namespace ainic;
@@ -33,7 +35,9 @@ extern "C" const char* ainic_version(void) { return "b200-ainic 0.1 (sm_100a)"; 
 
 struct ainic_comm {
   int rank = 0, nranks = 1, device = 0;
-  size_t heap_bytes = 0, bump = 0;
+  size_t heap_bytes = 0;
+  ainic::HeapAlloc alloc;                 // offsets inside heap: same sequence of calls = same offsets on every rank
+  std::vector<uint8_t*> retired;          // outgrown staging areas of a multi-rank communicator (see ensure_staging_frames)
   uint8_t* heap = nullptr;
   uint8_t* peer_base[kMaxRanks] = {};
   bool connected = false;
@@ -73,7 +77,8 @@ extern "C" int ainic_comm_create(ainic_comm_t** out, int rank, int nranks, size_
   c->flags = reinterpret_cast<uint32_t*>(c->heap);
   c->counters = reinterpret_cast<unsigned long long*>(c->heap + align_up(kFlagWords * sizeof(uint32_t), 4096));
   c->epoch_dev = reinterpret_cast<uint32_t*>(c->counters + 32);   // same zeroed page, past the counters
-  c->bump = reserved;
+  c->alloc.reset(c->heap_bytes);
+  c->alloc.alloc(reserved, 4096);          // flags / counters / call number: offset 0, never freed
   c->peer_base[rank] = c->heap;
   c->connected = (nranks == 1);
   if (const char* t = getenv("AINIC_TIMEOUT_MS")) c->timeout_ns = strtoull(t, nullptr, 10) * 1000000ull;
@@ -117,10 +122,41 @@ extern "C" int ainic_comm_destroy(ainic_comm_t* c) {
 extern "C" void* ainic_comm_alloc(ainic_comm_t* c, size_t bytes, size_t align) {
   if (!c || bytes == 0) return nullptr;
   if (align < 256) align = 256;
-  const size_t off = align_up(c->bump, align);
-  if (off + bytes > c->heap_bytes) { set_error("symmetric heap exhausted"); return nullptr; }
-  c->bump = off + bytes;
+  if (align & (align - 1)) { set_error("alignment must be a power of two"); return nullptr; }
+  const size_t off = c->alloc.alloc(bytes, align);
+  if (off == ainic::HeapAlloc::kNone) { set_error("symmetric heap exhausted"); return nullptr; }
   return c->heap + off;
+}
+
+// Returns a block to the heap (same call, in the same order, on every rank).  The caller guarantees that no
+// kernel that uses the block - on this rank or, through peer pointers, on another - is still running.
+extern "C" int ainic_comm_free(ainic_comm_t* c, void* ptr) {
+  if (!c || !ptr) return AINIC_ERR_ARG;
+  const uint8_t* p = static_cast<const uint8_t*>(ptr);
+  if (p <= c->heap || p >= c->heap + c->heap_bytes || !c->alloc.free((size_t)(p - c->heap))) {
+    set_error("ainic_comm_free: not a block of this heap");
+    return AINIC_ERR_ARG;
+  }
+  return AINIC_OK;
+}
+// Collective by contract: call on every rank after a barrier behind which no fused call is in flight anywhere.
+// Returns the outgrown staging areas to the heap; the number of blocks released.
+extern "C" int ainic_comm_release_retired(ainic_comm_t* c) {
+  if (!c) return AINIC_ERR_ARG;
+  cudaDeviceSynchronize();
+  const int n = (int)c->retired.size();
+  for (uint8_t* p : c->retired) ainic_comm_free(c, p);
+  c->retired.clear();
+  return n;
+}
+// out[0] bytes in use, out[1] high-water offset, out[2] free blocks below it, out[3] capacity
+extern "C" int ainic_comm_heap_stats(ainic_comm_t* c, size_t out[4]) {
+  if (!c || !out) return AINIC_ERR_ARG;
+  out[0] = c->alloc.bytes_in_use();
+  out[1] = c->alloc.high_water();
+  out[2] = c->alloc.free_blocks();
+  out[3] = c->heap_bytes;
+  return AINIC_OK;
 }
 
 extern "C" void* ainic_comm_peer_ptr(ainic_comm_t* c, const void* local_ptr, int peer) {
@@ -262,11 +298,27 @@ static int check_ring_limits(int nranks, size_t count, int ctas) {
 
 static int ensure_staging_frames(ainic_comm* c, size_t frames) {
   if (frames <= c->stage_frames) return AINIC_OK;
-  // Grow-only; every rank sees the same call sequence, so offsets stay symmetric.
+  // The staging area only grows.  The old one cannot be handed out again right away: a slower peer may still be
+  // pulling the previous call's shard from it, and nothing on this rank can know when that ends.  With one rank
+  // it is freed at once (after a device synchronise); otherwise it is retired and goes back to the heap in
+  // ainic_comm_release_retired(), which the caller invokes when every rank is known to be idle (barrier).
+  // Every rank sees the same call sequence, so offsets stay symmetric.
   const size_t want = frames;
+  if (c->stage_c) {
+    if (c->nranks == 1) {
+      cudaDeviceSynchronize();
+      ainic_comm_free(c, c->stage_c);
+      ainic_comm_free(c, c->stage_d);
+    } else {
+      c->retired.push_back(c->stage_c);
+      c->retired.push_back(c->stage_d);
+    }
+    c->stage_c = c->stage_d = nullptr;
+    c->stage_frames = 0;
+  }
   uint8_t* sc = static_cast<uint8_t*>(ainic_comm_alloc(c, 2 * want * 1024, 4096));
   uint8_t* sd = static_cast<uint8_t*>(ainic_comm_alloc(c, 2 * want * 2048 + kRingSlack, 4096));
-  if (!sc || !sd) return AINIC_ERR_ARG;
+  if (!sc || !sd) { if (sc) ainic_comm_free(c, sc); return AINIC_ERR_ARG; }
   c->stage_c = sc;
   c->stage_d = sd;
   c->stage_frames = want;

@@ -299,3 +299,23 @@ extern "C" void ainic_ref_init_buf(float* buf, size_t n, uint64_t seed, int init
     buf[i] = (float)(init_one ? 1.0 : (init_pos ? u : (0.05 - u / 10.0)));
   }
 }
+
+// ---------------------------------------------------------------- symmetric-heap offset allocator (csrc/comm/heap_alloc.h)
+// The allocator is plain host code; these hooks let the CPU test tier drive it without a GPU.
+#include "../comm/heap_alloc.h"
+extern "C" void* ainic_ref_heap_new(size_t capacity) {
+  auto* h = new ainic::HeapAlloc();
+  h->reset(capacity);
+  return h;
+}
+extern "C" void ainic_ref_heap_delete(void* h) { delete static_cast<ainic::HeapAlloc*>(h); }
+// returns the offset, or (size_t)-1 when the request does not fit
+extern "C" size_t ainic_ref_heap_alloc(void* h, size_t bytes, size_t align) { return static_cast<ainic::HeapAlloc*>(h)->alloc(bytes, align); }
+extern "C" int ainic_ref_heap_free(void* h, size_t off) { return static_cast<ainic::HeapAlloc*>(h)->free(off) ? 1 : 0; }
+// out[0] bytes in use, out[1] high-water offset, out[2] number of free blocks below it
+extern "C" void ainic_ref_heap_stats(void* h, size_t out[3]) {
+  auto* a = static_cast<ainic::HeapAlloc*>(h);
+  out[0] = a->bytes_in_use();
+  out[1] = a->high_water();
+  out[2] = a->free_blocks();
+}

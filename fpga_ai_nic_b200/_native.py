@@ -99,6 +99,13 @@ def oracle() -> C.CDLL:
     lib.ainic_ref_softmax_loss.restype = C.c_float
     lib.ainic_ref_softmax_loss.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_float]
     lib.ainic_ref_init_buf.argtypes = [vp, sz, C.c_uint64, C.c_int, C.c_int]
+    lib.ainic_ref_heap_new.restype = vp
+    lib.ainic_ref_heap_new.argtypes = [sz]
+    lib.ainic_ref_heap_delete.argtypes = [vp]
+    lib.ainic_ref_heap_alloc.restype = sz
+    lib.ainic_ref_heap_alloc.argtypes = [vp, sz, sz]
+    lib.ainic_ref_heap_free.argtypes = [vp, sz]
+    lib.ainic_ref_heap_stats.argtypes = [vp, vp]
     for fn, args, res in _NIC_SIGS:
         if hasattr(lib, fn):
             getattr(lib, fn).argtypes = args
@@ -167,6 +174,9 @@ def cuda() -> C.CDLL:
     lib.ainic_comm_destroy.argtypes = [vp]
     lib.ainic_comm_alloc.restype = vp
     lib.ainic_comm_alloc.argtypes = [vp, sz, sz]
+    lib.ainic_comm_free.argtypes = [vp, vp]
+    lib.ainic_comm_release_retired.argtypes = [vp]
+    lib.ainic_comm_heap_stats.argtypes = [vp, vp]
     lib.ainic_comm_peer_ptr.restype = vp
     lib.ainic_comm_peer_ptr.argtypes = [vp, vp, C.c_int]
     lib.ainic_comm_counters.argtypes = [vp, c_u64p]
@@ -194,6 +204,7 @@ def cuda() -> C.CDLL:
                                       C.c_float, C.c_int, C.c_int, C.c_int, C.c_int]
     lib.ainic_softmax_xent_f32.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_float, vp]
     lib.ainic_mlp_destroy.argtypes = [vp]
+    lib.ainic_mlp_destroy_ex.argtypes = [vp, C.c_int]
     lib.ainic_mlp_buffer.restype = vp
     lib.ainic_mlp_buffer.argtypes = [vp, C.c_int, C.c_int]
     lib.ainic_mlp_sync_shadows.argtypes = [vp, vp]

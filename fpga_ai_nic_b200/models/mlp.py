@@ -314,7 +314,21 @@ class MLPTrainer:
             self.buffer("bias", l).copy_(sd["biases"][l])
         self.sync_shadows()
 
-    def close(self) -> None:
+    def close(self, collective: bool = True) -> None:
+        """Destroy the native trainer.  Its weight / gradient arenas go back to the communicator's heap, so another
+        trainer can be built on the same communicator.  With more than one rank that needs every rank to be idle:
+        ``collective=True`` (default) runs a barrier first and must then be called on every rank; with
+        ``collective=False`` the arenas stay allocated until the communicator is destroyed."""
         if self.handle:
-            self.lib.ainic_mlp_destroy(self.handle)
+            free_heap = 1
+            if self.world > 1:
+                import torch.distributed as dist
+                if collective and dist.is_available() and dist.is_initialized():
+                    self.wait()
+                    torch.cuda.synchronize(self.device)
+                    dist.barrier()
+                else:
+                    free_heap = 0
+            self._views.clear()
+            self.lib.ainic_mlp_destroy_ex(self.handle, free_heap)
             self.handle = None

@@ -81,6 +81,27 @@ class Communicator:
             nbytes *= int(s)
         return tensor_from_ptr(self.alloc_ptr(nbytes), shape, dtype, owner=self, device=self.device)
 
+    def free(self, t) -> None:
+        """Return a block obtained from ``empty`` / ``alloc_ptr`` to the heap (a tensor or a raw pointer).  Same call in
+        the same order on every rank, and no kernel anywhere may still be using the block - with more than one rank
+        that means: behind a barrier.  The tensor must not be used afterwards."""
+        p = t.data_ptr() if isinstance(t, torch.Tensor) else int(t)
+        N.check(self.lib.ainic_comm_free(self.handle, p), "comm_free")
+
+    def trim(self, group=None) -> int:
+        """Collective: give staging areas that a larger bucket outgrew back to the heap (they are only retired while
+        a peer might still read them).  Synchronises the device and, with more than one rank, runs a barrier first."""
+        torch.cuda.synchronize(self.device)
+        if self.world_size > 1:
+            import torch.distributed as dist
+            dist.barrier(group=group)
+        return int(self.lib.ainic_comm_release_retired(self.handle))
+
+    def heap_stats(self) -> dict:
+        out = (C.c_size_t * 4)()
+        N.check(self.lib.ainic_comm_heap_stats(self.handle, out), "comm_heap_stats")
+        return {"in_use": out[0], "high_water": out[1], "free_blocks": out[2], "capacity": out[3]}
+
     def peer_ptr(self, t: torch.Tensor, peer: int) -> int:
         return self.lib.ainic_comm_peer_ptr(self.handle, t.data_ptr(), peer)
 

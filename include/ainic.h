@@ -153,6 +153,15 @@ int ainic_comm_destroy(ainic_comm_t* c);
  * offsets match (the reference's flat DMA-able buffers from fpga.allocBuffer,
  * sw/mlp_mpi_example_f32.cpp:396-401). */
 void* ainic_comm_alloc(ainic_comm_t* c, size_t bytes, size_t align);
+/* Returns a block to the heap: same call in the same order on every rank (the allocator is deterministic, so
+ * offsets stay symmetric), and no kernel anywhere may still use the block.  First fit with coalescing. */
+int ainic_comm_free(ainic_comm_t* c, void* ptr);
+/* Staging areas that a larger bucket outgrew are only retired on a multi-rank communicator (a peer may still be
+ * reading them); this returns them to the heap.  Call on every rank behind a barrier with no fused call in flight.
+ * Returns the number of blocks released. */
+int ainic_comm_release_retired(ainic_comm_t* c);
+/* out[0] bytes in use, out[1] high-water offset, out[2] free blocks below it, out[3] capacity */
+int ainic_comm_heap_stats(ainic_comm_t* c, size_t out[4]);
 void* ainic_comm_peer_ptr(ainic_comm_t* c, const void* local_ptr, int peer);
 int ainic_comm_rank(const ainic_comm_t* c);
 int ainic_comm_size(const ainic_comm_t* c);
@@ -268,6 +277,9 @@ int ainic_mlp_create(ainic_mlp_t** out, ainic_comm_t* comm, int nlayers, const i
 int ainic_mlp_create2(ainic_mlp_t** out, ainic_comm_t* comm, int nlayers, const int* sizes, int mb, int fuse, float lr,
                       float loss_weight, int codec, int bfp_mode, int algo, int compute_dtype);
 int ainic_mlp_destroy(ainic_mlp_t* m);
+/* free_heap != 0 also returns the weight / gradient arenas to the communicator's heap: only with one rank or behind a
+ * barrier with every rank idle, and with the same value on every rank (ainic_mlp_destroy: free_heap = one rank). */
+int ainic_mlp_destroy_ex(ainic_mlp_t* m, int free_heap);
 /* what: 0 weight f32, 1 grad f32, 2 shadow bf16, 3 bias f32, 4 dbias f32, 5 act bf16, 6 dact bf16, 7 relu mask */
 void* ainic_mlp_buffer(ainic_mlp_t* m, int what, int layer);
 int ainic_mlp_sync_shadows(ainic_mlp_t* m, void* stream);

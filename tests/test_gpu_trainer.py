@@ -293,3 +293,53 @@ def test_forward_mx_tracks_the_bf16_forward_and_the_weights():
     assert rel(ref1, ref0) > 0.01                        # the steps did move the weights
     assert rel(mx1, ref1) < 0.08 and rel(mx1, ref1) < rel(mx0, ref1)
     tr.close()
+
+
+def test_two_trainers_in_sequence_reuse_the_heap():
+    """The symmetric heap is a real allocator now: closing a trainer returns its arenas, so a second trainer fits
+    into a communicator sized for one (round 1's bump pointer would have been exhausted), lands on the same offsets
+    and trains to the same bits; a staging area outgrown by a larger call is freed on a single rank."""
+    from fpga_ai_nic_b200.models.mlp import MLPConfig, MLPTrainer
+    from fpga_ai_nic_b200.ops import kernels as K
+    from fpga_ai_nic_b200.parallel.comm import Communicator
+    cfg = MLPConfig(sizes=[512, 1024, 1024, 512], mb=256, fuse=0, lr=0.5, loss_weight=1.0)   # 2 M parameters: 22 MB of arenas
+    comm = Communicator(cfg.heap_bytes(1))                                                    # + 8 MiB of slack
+    base = comm.heap_stats()
+    g = torch.Generator().manual_seed(9)
+    x = K.cast_bf16((torch.rand(cfg.mb, cfg.sizes[0], generator=g) - 0.5).cuda())
+    y = torch.randint(0, cfg.sizes[-1], (cfg.mb,), generator=g, dtype=torch.int32).cuda()
+    outs, ptrs = [], []
+    for _ in range(3):                      # three trainers, one after the other, in a heap sized for one
+        tr = MLPTrainer(cfg, comm=comm)
+        ptrs.append(tr.buffer("weight", 0).data_ptr())
+        for _ in range(3):
+            tr.step(x, y)
+        tr.wait()
+        torch.cuda.synchronize()
+        tr.check_health()
+        outs.append([tr.buffer("weight", l).cpu().clone() for l in range(cfg.nlayers)])
+        tr.close()
+    assert ptrs[0] == ptrs[1] == ptrs[2]
+    for o in outs[1:]:
+        for a, b in zip(outs[0], o):
+            assert torch.equal(a, b)
+    after = comm.heap_stats()
+    assert after["in_use"] <= base["in_use"] + (8 << 20)     # only the communicator's staging is left
+    comm.close()
+    # staging growth on one rank: the outgrown area goes straight back to the heap
+    comm = Communicator(128 << 20)
+    small = comm.empty(1 << 16)
+    big = comm.empty(1 << 22)
+    w = torch.zeros(1 << 22, device="cuda")
+    s0 = comm.heap_stats()
+    comm.allreduce_fused(small, w[: 1 << 16], 0.1, codec=K.CODEC_BFP)
+    comm.allreduce_fused(big, w, 0.1, codec=K.CODEC_BFP)
+    comm.allreduce_fused(big, w, 0.1, codec=K.CODEC_BFP)
+    torch.cuda.synchronize()
+    s1 = comm.heap_stats()
+    frames = (1 << 22) // 512
+    assert s1["in_use"] - s0["in_use"] <= frames * 6144 + (2 << 20)      # one staging area, not the sum of all sizes
+    comm.free(big)
+    comm.free(small)
+    assert comm.heap_stats()["in_use"] == s1["in_use"] - (4 << 22) - (4 << 16)
+    comm.close()
