@@ -335,7 +335,7 @@ static size_t flow_staging_frames(const ainic_comm* c, size_t count, int nchunks
 extern "C" int ainic_comm_fill_ctx_(ainic_comm_t* c, RankCtx* out, const ainic_allreduce_args_t* a);
 
 // Size the internal staging for calls of up to `count` values now (same call on every rank), so the
-// first large bucket does not abandon a smaller staging area inside the grow-only heap.
+// first large bucket does not retire a smaller staging area (ensure_staging_frames).
 extern "C" int ainic_comm_reserve(ainic_comm_t* c, size_t count) {
   if (!c || count == 0) return AINIC_ERR_ARG;
   return ensure_staging(c, count);

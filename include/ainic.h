@@ -149,7 +149,7 @@ int ainic_comm_create(ainic_comm_t** out, int rank, int nranks, size_t heap_byte
 int ainic_comm_export(ainic_comm_t* c, void* handle_out /*64 B*/);
 int ainic_comm_connect(ainic_comm_t* c, const void* all_handles /*nranks*64 B, rank order*/);
 int ainic_comm_destroy(ainic_comm_t* c);
-/* Bump allocator inside the symmetric heap; every rank must allocate in the same order so that
+/* Allocation inside the symmetric heap (first fit, see ainic_comm_free); every rank must allocate in the same order so that
  * offsets match (the reference's flat DMA-able buffers from fpga.allocBuffer,
  * sw/mlp_mpi_example_f32.cpp:396-401). */
 void* ainic_comm_alloc(ainic_comm_t* c, size_t bytes, size_t align);

@@ -324,7 +324,7 @@ def test_two_trainers_in_sequence_reuse_the_heap():
         for a, b in zip(outs[0], o):
             assert torch.equal(a, b)
     after = comm.heap_stats()
-    assert after["in_use"] <= base["in_use"] + (8 << 20)     # only the communicator's staging is left
+    assert after["in_use"] <= base["in_use"] + (1024 * 1024 // 512) * 6144 + (1 << 20)     # only the communicator's staging (largest layer) is left
     comm.close()
     # staging growth on one rank: the outgrown area goes straight back to the heap
     comm = Communicator(128 << 20)
