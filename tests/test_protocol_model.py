@@ -182,3 +182,135 @@ def test_twoshot_alone_would_not_need_the_parity_halves():
     (and the GEMM-written buffers), which has no closing exchange - see the negative control above."""
     for seed in range(40):
         run(twoshot, 3, 2, 6, seed, parity=False)
+
+
+# ------------------------------------------------------------------------------------------ flow all-reduce
+# csrc/comm/flow.cuh: ONE persistent kernel per step.  Roles inside a rank run concurrently: the GEMMs (producer)
+# write chunk k's compressed frames and ring its doorbell; the forwarder turns doorbells into "readable" flags on
+# every rank; reduce warps wait for every rank's flag of chunk k, reduce their shard, publish it into stage D and
+# the LAST of them (ticket) posts "published"; gather warps wait for the peers' "published" flags and read the
+# peers' stage D.  Kernel boundaries are stream order: a rank's step e + 1 starts when all of its roles of step e
+# have finished.
+class FlowWorld:
+    def __init__(self, n, chunks, reducers, gatherers):
+        self.n, self.chunks, self.nr, self.ng = n, chunks, reducers, gatherers
+        self.cg = [[0] * chunks for _ in range(n)]              # [rank][chunk] = step whose frames the buffer holds
+        self.doorbell = [[0] * chunks for _ in range(n)]
+        self.ready = [[[0] * n for _ in range(chunks)] for _ in range(n)]     # [dst][chunk][src]
+        self.pub = [[[0] * n for _ in range(chunks)] for _ in range(n)]
+        self.stage_d = [[0] * chunks for _ in range(n)]
+        self.ticket = [[0] * chunks for _ in range(n)]
+        self.done_roles = [0] * n                               # roles of the current step that have finished
+        self.step = [1] * n
+
+
+def _flow_role(w, r, steps, body, nroles):
+    """Run `body(step)` once per step; a rank's roles advance to the next step together (kernel boundary)."""
+    for e in range(1, steps + 1):
+        while w.step[r] != e:
+            yield
+        yield from body(e)
+        w.done_roles[r] += 1
+        if w.done_roles[r] == nroles:
+            w.done_roles[r] = 0
+            w.step[r] = e + 1
+        yield
+
+
+def flow_coroutines(w, steps, wait_doorbell=True, wait_pub=True, last_warp_posts=True):
+    n, C = w.n, w.chunks
+    nroles = 2 + w.nr + w.ng
+    cos = []
+    for r in range(n):
+        def producer(e, r=r):
+            for k in range(C):
+                w.cg[r][k] = e
+                yield
+                w.doorbell[r][k] = e
+                yield
+
+        def forwarder(e, r=r):
+            for k in range(C):
+                while wait_doorbell and w.doorbell[r][k] < e:
+                    yield
+                for p in range(n):
+                    w.ready[p][k][r] = e
+                    yield
+
+        def reducer(e, r=r):
+            for k in range(C):
+                while any(w.ready[r][k][p] < e for p in range(n)):
+                    yield
+                for p in range(n):
+                    if w.cg[p][k] != e:
+                        raise Violation(f"rank {r} step {e} chunk {k}: frames of rank {p} belong to step {w.cg[p][k]}")
+                    yield
+                w.stage_d[r][k] = e          # (every reduce warp writes its own frames of the shard; one cell stands for them)
+                yield
+                w.ticket[r][k] += 1
+                last = w.ticket[r][k] == w.nr
+                if last:
+                    w.ticket[r][k] = 0
+                if last or not last_warp_posts:
+                    for p in range(n):
+                        if p != r:
+                            w.pub[p][k][r] = e
+                            yield
+
+        def gatherer(e, r=r):
+            for k in range(C):
+                while wait_pub and any(w.pub[r][k][p] < e for p in range(n) if p != r):
+                    yield
+                for p in range(n):
+                    if p != r:
+                        if w.stage_d[p][k] != e:
+                            raise Violation(f"rank {r} step {e} chunk {k}: stage D of rank {p} holds step {w.stage_d[p][k]}")
+                        yield
+
+        cos.append(_flow_role(w, r, steps, producer, nroles))
+        cos.append(_flow_role(w, r, steps, forwarder, nroles))
+        cos += [_flow_role(w, r, steps, reducer, nroles) for _ in range(w.nr)]
+        cos += [_flow_role(w, r, steps, gatherer, nroles) for _ in range(w.ng)]
+    return cos
+
+
+def run_flow_model(n, seed, steps=4, chunks=3, reducers=2, gatherers=2, **kw):
+    rng = random.Random(seed)
+    w = FlowWorld(n, chunks, reducers, gatherers)
+    live = flow_coroutines(w, steps, **kw)
+    weight = [rng.choice((1, 1, 5, 25)) for _ in live]
+    budget = 0
+    while live:
+        i = rng.choices(range(len(live)), weights=weight)[0]
+        try:
+            next(live[i])
+        except StopIteration:
+            live.pop(i)
+            weight.pop(i)
+        budget += 1
+        assert budget < 3_000_000, "deadlock in the model"
+
+
+@pytest.mark.parametrize("n", [2, 3, 4])
+def test_flow_protocol_has_no_race_and_no_deadlock(n):
+    for seed in range(25):
+        run_flow_model(n, seed)
+
+
+def test_flow_negative_controls_are_caught():
+    def caught(**kw):
+        hits = 0
+        for seed in range(40):
+            try:
+                run_flow_model(3, seed, **kw)
+            except Violation:
+                hits += 1
+        return hits
+    # a forwarder that does not wait for the GEMMs' doorbell announces frames that are not written yet
+    assert caught(wait_doorbell=False) > 0
+    # gather warps that do not wait for "published" read the previous step's shard
+    assert caught(wait_pub=False) > 0
+    # if every reduce warp posted "published" instead of only the last one (the ticket), a peer could finish the step
+    # while slower reduce warps of this rank are still reading that peer's frames - and its next step's GEMMs
+    # overwrite them (the model keeps ONE frame buffer per rank; the real trainer alternates two, which is margin)
+    assert caught(last_warp_posts=False) > 0
